@@ -1,0 +1,500 @@
+// Grouped bf16 GEMM for sm_100a: D[M,N] = A[M,K] * B[N,K]^T with fused training epilogues.
+//
+//   * operands arrive by TMA (cp.async.bulk.tensor, 128-byte swizzle) into a multi-stage smem ring,
+//   * one elected thread issues tcgen05.mma (cta_group::1, M=128, N=block_n, K=16 per instruction),
+//   * the fp32 accumulator lives in TMEM and is read back with tcgen05.ld by four epilogue warps,
+//   * the epilogue fuses bias + ELU/ReLU + Philox dropout (forward), the activation/dropout
+//     derivative (dgrad), the fp32 scale-and-store into the flat gradient buffer (wgrad) or the whole
+//     sparse-softmax cross-entropy + top-1 + dlogits (output layer),
+//   * up to four independent problems ride in one launch (e.g. dgrad + wgrad of a layer).
+//
+// What it reproduces: MatMul/BiasAdd/Elu/dropout of forward_propagation (reference
+// distribute_training.py:53-61), SparseSoftmaxCrossEntropyWithLogits + mean (:80-82), in_top_k (:96)
+// and their gradients as created by opt.minimize (:152).
+#include <math.h>
+#include <atomic>
+#include <stdio.h>
+#include <string.h>
+
+#include "../include/ttd_b200.h"
+#include "common.cuh"
+
+namespace ttd {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;                       // 64 bf16 = 128 B = one swizzle row
+constexpr int kAStageBytes = kBlockM * kBlockK * 2;  // 16 KiB
+constexpr int kMaxProblems = 4;
+constexpr int kThreads = 256;                     // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps4-7 epilogue
+
+struct GemmProblem {
+  CUtensorMap tma_a;
+  CUtensorMap tma_b;
+  int M, N, K;
+  int block_n;
+  int tiles_m, tiles_n;
+  int tile_begin;
+  int mode;
+  int act;
+  float drop_rate;
+  uint32_t layer_id;
+  const float* bias;
+  __nv_bfloat16* out;
+  long long ldo;
+  __nv_bfloat16* outT;
+  long long ldt;
+  float* outf;
+  long long ldf;
+  const __nv_bfloat16* aux;
+  long long ldaux;
+  float scale;
+  const long long* labels;
+  float* metrics;
+};
+
+struct GemmGroup {
+  GemmProblem p[kMaxProblems];
+  int count;
+  uint32_t seed_lo, seed_hi;
+  const unsigned long long* step_ptr;
+  int stages;
+  int b_stage_bytes;
+  int tmem_cols;
+  int use_pdl;
+};
+
+__device__ __forceinline__ void store_bf16x8(__nv_bfloat16* dst, const float* v) {
+  uint4 u;
+  __nv_bfloat162 t;
+  t = __floats2bfloat162_rn(v[0], v[1]); u.x = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[2], v[3]); u.y = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[4], v[5]); u.z = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[6], v[7]); u.w = *reinterpret_cast<uint32_t*>(&t);
+  *reinterpret_cast<uint4*>(dst) = u;
+}
+
+// Write 16 consecutive columns [n0, n0+16) of row m: row-major bf16 (16-byte stores where the padded
+// row allows it) and/or the transposed copy (coalesced across the warp because lane == row).
+__device__ __forceinline__ void store_row_chunk(const GemmProblem& P, int m, int n0, const float* v) {
+  if (P.out != nullptr) {
+    __nv_bfloat16* row = P.out + static_cast<long long>(m) * P.ldo;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int nb = n0 + 8 * h;
+      if (nb + 8 <= P.ldo) {
+        store_bf16x8(row + nb, v + 8 * h);  // pad columns (n >= N) receive the zeros prepared by the caller
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (nb + j < P.N) row[nb + j] = __float2bfloat16(v[8 * h + j]);
+      }
+    }
+  }
+  if (P.outT != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+      if (n0 + j < P.N) P.outT[static_cast<long long>(n0 + j) * P.ldt + m] = __float2bfloat16(v[j]);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_constant__ GemmGroup g) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int stages = g.stages;
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + stages * kAStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sB + stages * g.b_stage_bytes);
+  uint64_t* empty_bar = full_bar + stages;
+  uint64_t* tmem_full_bar = empty_bar + stages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // which problem / tile does this CTA own?
+  int pi = 0;
+#pragma unroll
+  for (int i = 1; i < kMaxProblems; ++i)
+    if (i < g.count && static_cast<int>(blockIdx.x) >= g.p[i].tile_begin) pi = i;
+  const GemmProblem& P = g.p[pi];
+  const int tile = blockIdx.x - P.tile_begin;
+  const int tile_m = tile % P.tiles_m;
+  const int tile_n = tile / P.tiles_m;
+  const int m0 = tile_m * kBlockM;
+  const int nbase = tile_n * P.block_n;
+  const int num_kb = (P.K + kBlockK - 1) / kBlockK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&P.tma_a);
+    tma_prefetch_desc(&P.tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, static_cast<uint32_t>(g.tmem_cols));
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // Everything above overlaps the previous kernel's tail under programmatic dependent launch;
+  // nothing below may touch global memory before the dependency resolves.
+  if (g.use_pdl) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  }
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      const uint32_t tx_bytes = kAStageBytes + P.block_n * kBlockK * 2;
+      int s = 0;
+      uint32_t ph = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[s], ph ^ 1u);
+        mbar_arrive_expect_tx(&full_bar[s], tx_bytes);
+        tma_load_2d(sA + s * kAStageBytes, &P.tma_a, &full_bar[s], kb * kBlockK, m0);
+        tma_load_2d(sB + s * g.b_stage_bytes, &P.tma_b, &full_bar[s], kb * kBlockK, nbase);
+        if (++s == stages) { s = 0; ph ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(kBlockM, static_cast<uint32_t>(P.block_n));
+      int s = 0;
+      uint32_t ph = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(sA + s * kAStageBytes);
+        const uint32_t b_addr = smem_u32(sB + s * g.b_stage_bytes);
+#pragma unroll
+        for (int k = 0; k < kBlockK / 16; ++k) {
+          const uint64_t da = umma_desc_k_sw128(a_addr + k * 32);
+          const uint64_t db = umma_desc_k_sw128(b_addr + k * 32);
+          umma_bf16_ss(tmem_base, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);  // smem slot reusable once these MMAs have drained
+        if (++s == stages) { s = 0; ph ^= 1u; }
+      }
+      umma_commit(tmem_full_bar);  // accumulator complete
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue: TMEM -> registers -> global =====================
+    const int quad = warp & 3;  // TMEM lane quadrant this warp may read
+    const int m = m0 + quad * 32 + lane;
+    const bool row_ok = m < P.M;
+    const unsigned long long step = g.step_ptr != nullptr ? *g.step_ptr : 0ull;
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const uint32_t taddr_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+    const int nchunks = P.block_n / 16;
+    float v[16];
+
+    if (P.mode == TTD_EPI_FWD_XENT) {
+      // One thread owns one example's whole logit row (N <= block_n). Three cheap passes over TMEM.
+      const long long label = row_ok ? P.labels[m] : 0;
+      float zmax = -INFINITY, zlab = 0.0f;
+      for (int c = 0; c < nchunks; ++c) {
+        __syncwarp();
+        tmem_ld16(taddr_row + c * 16, v);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int n = c * 16 + j;
+          if (n < P.N) {
+            const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
+            zmax = fmaxf(zmax, z);
+            if (n == label) zlab = z;
+          }
+        }
+      }
+      float sum = 0.0f;
+      int greater = 0;
+      for (int c = 0; c < nchunks; ++c) {
+        __syncwarp();
+        tmem_ld16(taddr_row + c * 16, v);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int n = c * 16 + j;
+          if (n < P.N) {
+            const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
+            sum += __expf(z - zmax);
+            greater += (z > zlab) ? 1 : 0;
+          }
+        }
+      }
+      const float inv_sum = 1.0f / sum;
+      const float gscale = P.scale / static_cast<float>(P.M);
+      for (int c = 0; c < nchunks; ++c) {
+        __syncwarp();
+        tmem_ld16(taddr_row + c * 16, v);
+        float d[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int n = c * 16 + j;
+          float dz = 0.0f;
+          if (n < P.N) {
+            const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
+            if (row_ok && P.outf) P.outf[static_cast<long long>(m) * P.ldf + n] = z;
+            dz = (__expf(z - zmax) * inv_sum - (n == label ? 1.0f : 0.0f)) * gscale;
+          }
+          d[j] = dz;
+        }
+        if (row_ok) store_row_chunk(P, m, c * 16, d);
+      }
+      float loss = row_ok ? (__logf(sum) + zmax - zlab) / static_cast<float>(P.M) : 0.0f;
+      float corr = (row_ok && greater < 1) ? 1.0f / static_cast<float>(P.M) : 0.0f;
+      loss = warp_sum(loss);
+      corr = warp_sum(corr);
+      if (lane == 0 && P.metrics) {
+        atomicAdd(&P.metrics[0], loss);
+        atomicAdd(&P.metrics[1], corr);
+      }
+    } else {
+      const float keep = 1.0f - P.drop_rate;
+      const float inv_keep = 1.0f / keep;
+      const uint32_t drop_thresh = static_cast<uint32_t>(fminf(P.drop_rate, 1.0f) * 4294967040.0f);
+      for (int c = 0; c < nchunks; ++c) {
+        const int n0 = nbase + c * 16;
+        __syncwarp();                      // tcgen05.ld is warp-collective: reconverge before it
+        tmem_ld16(taddr_row + c * 16, v);
+        const bool live = row_ok && n0 < P.N;
+        if (live && P.mode == TTD_EPI_WGRAD) {
+          float* row = P.outf + static_cast<long long>(m) * P.ldf;
+          const bool vec = ((reinterpret_cast<uintptr_t>(row + n0) & 15u) == 0) && (n0 + 16 <= P.N);
+          if (vec) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              *reinterpret_cast<float4*>(row + n0 + 4 * q) =
+                  make_float4(v[4 * q] * P.scale, v[4 * q + 1] * P.scale, v[4 * q + 2] * P.scale,
+                              v[4 * q + 3] * P.scale);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (n0 + j < P.N) row[n0 + j] = v[j] * P.scale;
+          }
+        } else if (live) {
+          float a_saved[16];
+          if (P.mode == TTD_EPI_DGRAD && P.aux != nullptr) {
+            const __nv_bfloat16* arow = P.aux + static_cast<long long>(m) * P.ldaux;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) a_saved[j] = (n0 + j < P.N) ? __bfloat162float(arow[n0 + j]) : 0.0f;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) a_saved[j] = 1.0f;
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            Philox4 rnd{0, 0, 0, 0};
+            if (P.drop_rate > 0.0f)
+              rnd = dropout_block(static_cast<uint32_t>(m), static_cast<uint32_t>((n0 >> 2) + q), step, P.layer_id,
+                                  g.seed_lo, g.seed_hi);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int j = 4 * q + i;
+              const int n = n0 + j;
+              float r = 0.0f;
+              if (n < P.N) {
+                const bool kept = (P.drop_rate <= 0.0f) || (philox_pick(rnd, i) >= drop_thresh);
+                if (P.mode == TTD_EPI_FWD) {
+                  const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
+                  const float a = act_apply(z, P.act);
+                  if (P.outf) P.outf[static_cast<long long>(m) * P.ldf + n] = a;
+                  r = kept ? a * inv_keep : 0.0f;
+                } else {  // DGRAD
+                  const float a = a_saved[j] * keep;  // undo the 1/keep scaling of the saved activation
+                  r = kept ? v[j] * inv_keep * act_grad_from_out(a, P.act) : 0.0f;
+                }
+              }
+              v[j] = r;
+            }
+          }
+          store_row_chunk(P, m, n0, v);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, static_cast<uint32_t>(g.tmem_cols));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || p == nullptr) {
+    set_error("cuTensorMapEncodeTiled not available from the driver (%s)", cudaGetErrorString(e));
+    return nullptr;
+  }
+  fn = reinterpret_cast<EncodeTiledFn>(p);
+  return fn;
+}
+
+// bf16 [rows, ld] matrix with `cols` valid elements per row; box = {64, box_rows}, 128-B swizzle,
+// out-of-bounds elements read as zero (this is what pads K=784 / N=200 / M=785 to tile multiples).
+static int make_tmap(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return -2;
+  if ((reinterpret_cast<uintptr_t>(base) & 15u) != 0 || (ld % 8) != 0) {
+    set_error("TMA operand must be 16-byte aligned with ld %% 8 == 0 (base=%p ld=%lld)", base, (long long)ld);
+    return -3;
+  }
+  cuuint64_t gdim[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t gstride[1] = {static_cast<cuuint64_t>(ld) * 2};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(kBlockK), static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed: CUresult %d (rows=%lld cols=%lld ld=%lld box_rows=%d)", (int)r,
+              (long long)rows, (long long)cols, (long long)ld, box_rows);
+    return -4;
+  }
+  return 0;
+}
+
+static int choose_block_n(int M, int N) {
+  // Wide layers: keep >= ~1 wave of CTAs streaming the weight matrix; small layers: one tile.
+  const int tiles_m = (M + kBlockM - 1) / kBlockM;
+  int bn = 256;
+  while (bn > 16 && tiles_m * ((N + bn - 1) / bn) < 120) bn >>= 1;
+  const int n16 = ((N + 15) / 16) * 16;
+  if (bn > n16) bn = n16;
+  if (bn < 16) bn = 16;
+  return bn;
+}
+
+extern std::atomic<uint64_t> g_launch_count;
+
+}  // namespace ttd
+
+using namespace ttd;
+
+extern "C" int ttd_gemm_group(const TtdGemmDesc* d, int count, uint64_t seed, const uint64_t* step_ptr,
+                              uint32_t flags, void* stream) {
+  if (count < 1 || count > kMaxProblems) {
+    set_error("ttd_gemm_group: count must be in [1,%d], got %d", kMaxProblems, count);
+    return -1;
+  }
+  GemmGroup g;
+  memset(&g, 0, sizeof(g));
+  g.count = count;
+  g.seed_lo = static_cast<uint32_t>(seed);
+  g.seed_hi = static_cast<uint32_t>(seed >> 32);
+  g.step_ptr = reinterpret_cast<const unsigned long long*>(step_ptr);
+  g.use_pdl = (flags & 1u) ? 1 : 0;
+  int total_tiles = 0, max_bn = 16;
+  for (int i = 0; i < count; ++i) {
+    const TtdGemmDesc& s = d[i];
+    GemmProblem& P = g.p[i];
+    if (s.M < 1 || s.N < 1 || s.K < 1) {
+      set_error("ttd_gemm_group: problem %d has empty shape %dx%dx%d", i, s.M, s.N, s.K);
+      return -1;
+    }
+    int bn = s.block_n > 0 ? s.block_n : choose_block_n(s.M, s.N);
+    if (bn % 16 != 0 || bn < 16 || bn > 256) {
+      set_error("ttd_gemm_group: block_n must be a multiple of 16 in [16,256], got %d", bn);
+      return -1;
+    }
+    if (s.mode == TTD_EPI_FWD_XENT) {
+      bn = ((s.N + 15) / 16) * 16;
+      if (bn > 256 || s.labels == nullptr) {
+        set_error("ttd_gemm_group: fused xent needs N <= 256 and labels");
+        return -1;
+      }
+    }
+    if (s.mode == TTD_EPI_WGRAD && s.outf == nullptr) {
+      set_error("ttd_gemm_group: wgrad needs outf");
+      return -1;
+    }
+    if (s.mode == TTD_EPI_DGRAD && s.aux == nullptr && (s.act != TTD_ACT_NONE || s.drop_rate > 0.f)) {
+      set_error("ttd_gemm_group: dgrad with activation/dropout needs aux");
+      return -1;
+    }
+    if ((s.out && (s.ldo % 8 != 0 || (reinterpret_cast<uintptr_t>(s.out) & 15u))) ) {
+      set_error("ttd_gemm_group: out must be 16-byte aligned with ldo %% 8 == 0");
+      return -1;
+    }
+    int rc = make_tmap(&P.tma_a, s.a, s.M, s.K, s.lda, kBlockM);
+    if (rc) return rc;
+    rc = make_tmap(&P.tma_b, s.b, s.N, s.K, s.ldb, bn);
+    if (rc) return rc;
+    P.M = s.M; P.N = s.N; P.K = s.K;
+    P.block_n = bn;
+    P.tiles_m = (s.M + kBlockM - 1) / kBlockM;
+    P.tiles_n = (s.N + bn - 1) / bn;
+    P.tile_begin = total_tiles;
+    total_tiles += P.tiles_m * P.tiles_n;
+    P.mode = s.mode; P.act = s.act; P.drop_rate = s.drop_rate; P.layer_id = s.layer_id;
+    P.bias = s.bias;
+    P.out = static_cast<__nv_bfloat16*>(s.out); P.ldo = s.ldo;
+    P.outT = static_cast<__nv_bfloat16*>(s.outT); P.ldt = s.ldt;
+    P.outf = s.outf; P.ldf = s.ldf;
+    P.aux = static_cast<const __nv_bfloat16*>(s.aux); P.ldaux = s.ldaux;
+    P.scale = s.scale;
+    P.labels = reinterpret_cast<const long long*>(s.labels);
+    P.metrics = s.metrics;
+    if (bn > max_bn) max_bn = bn;
+  }
+  g.b_stage_bytes = max_bn * kBlockK * 2;
+  if (g.b_stage_bytes < 1024) g.b_stage_bytes = 1024;
+  const int stage_bytes = kAStageBytes + g.b_stage_bytes;
+  int stages = (200 * 1024) / stage_bytes;
+  if (stages > 8) stages = 8;
+  if (stages < 2) stages = 2;
+  g.stages = stages;
+  int tmem_cols = 32;
+  while (tmem_cols < max_bn) tmem_cols <<= 1;
+  g.tmem_cols = tmem_cols;
+  const size_t smem_bytes = static_cast<size_t>(stages) * stage_bytes + 1024 + 256;
+
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  TTD_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    TTD_CUDA(cudaFuncSetAttribute(gemm_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set[dev] = true;
+  }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(static_cast<unsigned>(total_tiles));
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  int nattr = 0;
+  if (g.use_pdl) {
+    attr[nattr].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[nattr].val.programmaticStreamSerializationAllowed = 1;
+    ++nattr;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = nattr;
+  TTD_CUDA(cudaLaunchKernelEx(&cfg, gemm_group_kernel, g));
+  g_launch_count.fetch_add(1);
+  return 0;
+}

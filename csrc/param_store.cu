@@ -1,0 +1,336 @@
+// Parameter-store kernels: the "ps" side of the reference, executed by the GPU that owns a shard.
+//
+//   param_kernel<kInit>    He / variance-scaling truncated-normal init (reference :49, A.5), zero biases
+//   param_kernel<kRefresh> rebuild the bf16 compute copies from the fp32 master (after a restore)
+//   param_kernel<kUpdate>  the fused gradient push:
+//        [cross-GPU barrier: all replicas' gradients are in their symmetric buffers]
+//        g   = grad_scale * sum_r grad_r            (peer loads over NVLink, or one multimem.ld_reduce
+//                                                    that lets the NVSwitch do the sum: NVLS)
+//        g  += L2/L1 term on regularised kernels    (reference :50, :55)
+//        lr  = lr0 * decay^floor(gs/decay_steps)    (reference :136-140, read from the device global_step)
+//        w  -= lr * g                               (reference :150-152, ApplyGradientDescent on the ps)
+//        s  -= (1-d)(s-w), d=min(decay,(1+n)/(10+n)) (reference :153-161 dead code, north-star EMA)
+//        bf16 compute copies (both layouts) stored into EVERY replica's buffers (the parameter pull
+//        for all layers but the first, whose pull is fused into its GEMM)
+//        [cross-GPU barrier: every replica holds the new parameters]
+//        last block: ++global_step, ++local_step, publish + clear the metric accumulators
+//
+// The flat fp32 buffers hold one group per dense layer: kernel [rows, cols] immediately followed by
+// bias [cols], i.e. a [rows+1, cols] matrix, which is also exactly what the wgrad GEMM writes.
+#include <atomic>
+#include <math.h>
+#include <string.h>
+
+#include "../include/ttd_b200.h"
+#include "common.cuh"
+
+namespace ttd {
+
+extern std::atomic<uint64_t> g_launch_count;
+
+constexpr int kMaxVars = 16;
+constexpr int kMaxPeers = 8;
+constexpr int kTile = 32;
+
+struct VarTable {
+  TtdVarDesc v[kMaxVars];
+  int tile_begin[kMaxVars + 1];
+  int n;
+};
+
+struct PeerInfo {
+  const float* grads[kMaxPeers];     // gradient buffer of every replica (peer-mapped)
+  long long copy_delta[kMaxPeers];   // byte offset from a local bf16-copy pointer to replica r's copy
+  uint32_t* flags[kMaxPeers];        // signal pad of every replica: [grid][kMaxPeers] u32
+  const float* grads_mc;             // multicast mapping of the gradient buffer (NVLS) or NULL
+  int n_grads;                       // replicas contributing gradients
+  int n_copies;                      // replicas receiving the bf16 copies
+  int rank;
+  int barrier;                       // 1: run the cross-GPU barriers
+};
+
+enum { kInit = 0, kRefresh = 1, kUpdate = 2 };
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Block-wise barrier across replicas: block b of every replica meets block b of all others.
+// Writes made by this block before the call are visible to the peers' block b after it.
+__device__ __forceinline__ void replica_barrier(const PeerInfo& pi, uint32_t epoch) {
+  __syncthreads();
+  const int t = threadIdx.x;
+  const int n = pi.n_grads;
+  if (t < n) {
+    st_release_sys(pi.flags[t] + blockIdx.x * kMaxPeers + pi.rank, epoch);
+    const uint32_t* mine = pi.flags[pi.rank] + blockIdx.x * kMaxPeers + t;
+    const uint64_t t0 = globaltimer_ns();
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) {
+      if (globaltimer_ns() - t0 > 20000000000ull) __trap();  // a dead peer raises instead of hanging
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const float* mc_addr) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(mc_addr)
+               : "memory");
+  return r;
+}
+
+__device__ __forceinline__ float trunc_normal(uint64_t seed, uint64_t idx) {
+  // Philox + Box-Muller, resampled until |z| <= 2 (TF truncated_normal), deterministic in (seed, idx)
+  for (uint32_t attempt = 0; attempt < 16; ++attempt) {
+    const Philox4 p = philox4x32_10(static_cast<uint32_t>(idx), static_cast<uint32_t>(idx >> 32), attempt, 0x7F4A7C15u,
+                                    static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+    const float u1 = u32_to_unit_float(p.x), u2 = u32_to_unit_float(p.y);
+    const float rad = sqrtf(-2.0f * logf(u1));
+    const float z0 = rad * cosf(6.28318530718f * u2);
+    if (fabsf(z0) <= 2.0f) return z0;
+    const float z1 = rad * sinf(6.28318530718f * u2);
+    if (fabsf(z1) <= 2.0f) return z1;
+  }
+  return 0.0f;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarTable vt, float* __restrict__ w,
+                                                    float* __restrict__ ema, const __grid_constant__ PeerInfo pi,
+                                                    long long lo, long long hi, TtdHyper h, TtdStepState* st,
+                                                    int bump_global_step, unsigned long long seed) {
+  __shared__ float tile[kTile][kTile + 1];
+  __shared__ unsigned char tile_ok[kTile][kTile + 1];
+  __shared__ float s_lr, s_ema_d;
+  __shared__ unsigned long long s_lstep;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (MODE == kUpdate) {
+    if (threadIdx.x == 0) {
+      const long long gs = st->global_step;
+      double e = static_cast<double>(gs) / static_cast<double>(h.decay_steps);
+      if (h.staircase) e = floor(e);
+      s_lr = static_cast<float>(static_cast<double>(h.lr0) * pow(static_cast<double>(h.decay_rate), e));
+      const double n = static_cast<double>(gs + 1);
+      double d = h.ema_decay;
+      if (h.ema_warmup) d = fmin(d, (1.0 + n) / (10.0 + n));
+      s_ema_d = static_cast<float>(d);
+      s_lstep = st->local_step;
+    }
+    __syncthreads();
+    if (pi.barrier) replica_barrier(pi, static_cast<uint32_t>(2 * s_lstep + 1));
+  }
+  const float lr = s_lr, ema_d = s_ema_d;
+
+  const int total_tiles = vt.tile_begin[vt.n];
+  for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    int vi = 0;
+    for (int i = 1; i < vt.n; ++i)
+      if (t >= vt.tile_begin[i]) vi = i;
+    const TtdVarDesc& V = vt.v[vi];
+    const int R = V.rows + 1, C = V.cols;
+    const int tiles_c = (C + kTile - 1) / kTile;
+    const int lt = t - vt.tile_begin[vi];
+    const int r0 = (lt / tiles_c) * kTile, c0 = (lt % tiles_c) * kTile;
+    // quick reject: tile entirely outside [lo, hi)
+    const long long t_lo = V.offset + static_cast<long long>(r0) * C;
+    const long long t_hi = V.offset + static_cast<long long>(min(r0 + kTile, R)) * C;
+    if (t_hi <= lo || t_lo >= hi) continue;
+
+    __syncthreads();  // previous tile's transposed reads are done
+#pragma unroll
+    for (int rr = 0; rr < kTile / 8; ++rr) {
+      const int rl = warp + 8 * rr;
+      const int r = r0 + rl, c = c0 + lane;
+      bool ok = false;
+      float val = 0.0f;
+      if (r < R && c < C) {
+        const long long idx = V.offset + static_cast<long long>(r) * C + c;
+        if (idx >= lo && idx < hi) {
+          ok = true;
+          if (MODE == kInit) {
+            val = (r < V.rows) ? trunc_normal(seed, static_cast<uint64_t>(idx)) * sqrtf(2.6f / static_cast<float>(V.rows))
+                               : 0.0f;
+            w[idx] = val;
+            if (ema) ema[idx] = val;
+          } else if (MODE == kRefresh) {
+            val = w[idx];
+          } else {
+            float g = 0.0f;
+#pragma unroll 1
+            for (int q = 0; q < pi.n_grads; ++q) g += pi.grads[q][idx];
+            g *= h.grad_scale;
+            const float wv = w[idx];
+            if (V.regularize && r < V.rows) {
+              if (h.reg_kind == 2) g += h.reg_scale * wv;
+              else if (h.reg_kind == 1) g += h.reg_scale * (wv > 0.0f ? 1.0f : (wv < 0.0f ? -1.0f : 0.0f));
+            }
+            val = wv - lr * g;
+            w[idx] = val;
+            if (ema != nullptr && h.ema_decay > 0.0f) {
+              const float s = ema[idx];
+              ema[idx] = s - (1.0f - ema_d) * (s - val);
+            }
+          }
+          if (V.w_rm != nullptr && r < V.rows) {
+            const __nv_bfloat16 b = __float2bfloat16(val);
+            for (int q = 0; q < pi.n_copies; ++q) {
+              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(V.w_rm) + pi.copy_delta[q]);
+              dst[static_cast<long long>(r) * V.ld_rm + c] = b;
+            }
+          }
+        }
+      }
+      tile[rl][lane] = val;
+      tile_ok[rl][lane] = ok ? 1 : 0;
+    }
+    if (V.w_t != nullptr) {
+      __syncthreads();
+#pragma unroll
+      for (int cc = 0; cc < kTile / 8; ++cc) {
+        const int cl = warp + 8 * cc;
+        const int c = c0 + cl, r = r0 + lane;
+        if (tile_ok[lane][cl] && r < V.rows && c < C) {
+          const __nv_bfloat16 b = __float2bfloat16(tile[lane][cl]);
+          for (int q = 0; q < pi.n_copies; ++q) {
+            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(V.w_t) + pi.copy_delta[q]);
+            dst[static_cast<long long>(c) * V.ld_t + r] = b;
+          }
+        }
+      }
+    }
+  }
+
+  if (MODE == kUpdate) {
+    if (pi.barrier) {
+      __threadfence_system();
+      replica_barrier(pi, static_cast<uint32_t>(2 * s_lstep + 2));
+    }
+    // the last block to finish advances the step counters (nobody reads them any more in this launch)
+    __shared__ unsigned int s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(&st->done_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+    __syncthreads();
+    if (s_last && threadIdx.x == 0) {
+      st->done_counter = 0;
+      if (bump_global_step) st->global_step += 1;
+      st->local_step += 1;
+      st->lr_last = lr;
+      st->metrics_out[0] = st->metrics_acc[0];
+      st->metrics_out[1] = st->metrics_acc[1];
+      st->metrics_acc[0] = 0.0f;
+      st->metrics_acc[1] = 0.0f;
+      __threadfence();
+    }
+  }
+}
+
+static int build_table(VarTable* vt, const TtdVarDesc* vars, int nvars) {
+  if (nvars < 1 || nvars > kMaxVars) {
+    set_error("variable table holds 1..%d groups, got %d", kMaxVars, nvars);
+    return -1;
+  }
+  memset(vt, 0, sizeof(*vt));
+  vt->n = nvars;
+  int acc = 0;
+  for (int i = 0; i < nvars; ++i) {
+    vt->v[i] = vars[i];
+    vt->tile_begin[i] = acc;
+    const int tr = (vars[i].rows + 1 + kTile - 1) / kTile, tc = (vars[i].cols + kTile - 1) / kTile;
+    acc += tr * tc;
+  }
+  vt->tile_begin[nvars] = acc;
+  return 0;
+}
+
+static int grid_for(int total_tiles) {
+  const int cap = 148 * 8;
+  return total_tiles < cap ? total_tiles : cap;
+}
+
+}  // namespace ttd
+
+using namespace ttd;
+
+extern "C" int ttd_init_params(float* w, float* ema, const TtdVarDesc* vars, int nvars, uint64_t seed,
+                               void* stream) {
+  VarTable vt;
+  int rc = build_table(&vt, vars, nvars);
+  if (rc) return rc;
+  PeerInfo pi;
+  memset(&pi, 0, sizeof(pi));
+  pi.n_copies = 1;
+  TtdHyper h;
+  memset(&h, 0, sizeof(h));
+  const long long hi = vars[nvars - 1].offset + static_cast<long long>(vars[nvars - 1].rows + 1) * vars[nvars - 1].cols;
+  param_kernel<kInit><<<grid_for(vt.tile_begin[vt.n]), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      vt, w, ema, pi, 0, hi, h, nullptr, 0, seed);
+  TTD_CUDA(cudaGetLastError());
+  g_launch_count.fetch_add(1);
+  return 0;
+}
+
+extern "C" int ttd_refresh_copies(const float* w, const TtdVarDesc* vars, int nvars, void* stream) {
+  VarTable vt;
+  int rc = build_table(&vt, vars, nvars);
+  if (rc) return rc;
+  PeerInfo pi;
+  memset(&pi, 0, sizeof(pi));
+  pi.n_copies = 1;
+  TtdHyper h;
+  memset(&h, 0, sizeof(h));
+  const long long hi = vars[nvars - 1].offset + static_cast<long long>(vars[nvars - 1].rows + 1) * vars[nvars - 1].cols;
+  param_kernel<kRefresh><<<grid_for(vt.tile_begin[vt.n]), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      vt, const_cast<float*>(w), nullptr, pi, 0, hi, h, nullptr, 0, 0);
+  TTD_CUDA(cudaGetLastError());
+  g_launch_count.fetch_add(1);
+  return 0;
+}
+
+extern "C" int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars, int nvars, int64_t lo, int64_t hi,
+                                const TtdHyper* hyper, const TtdPeers* peers, TtdStepState* state,
+                                int32_t bump_global_step, void* stream) {
+  VarTable vt;
+  int rc = build_table(&vt, vars, nvars);
+  if (rc) return rc;
+  if (peers == nullptr || peers->n_grads < 1 || peers->n_grads > kMaxPeers || peers->n_copies < 1 ||
+      peers->n_copies > kMaxPeers) {
+    set_error("ttd_apply_update: need 1..%d gradient sources and copy targets", kMaxPeers);
+    return -1;
+  }
+  PeerInfo pi;
+  memset(&pi, 0, sizeof(pi));
+  for (int i = 0; i < kMaxPeers; ++i) {
+    pi.grads[i] = peers->grads[i];
+    pi.copy_delta[i] = peers->copy_delta[i];
+    pi.flags[i] = peers->flags[i];
+  }
+  pi.grads_mc = peers->grads_mc;
+  pi.n_grads = peers->n_grads;
+  pi.n_copies = peers->n_copies;
+  pi.rank = peers->rank;
+  pi.barrier = peers->barrier;
+  int grid = grid_for(vt.tile_begin[vt.n]);
+  if (pi.barrier) {
+    // blocks of different replicas wait on one another: all of them must be resident at once
+    if (peers->grid <= 0 || peers->grid > 148) {
+      set_error("ttd_apply_update: barrier mode needs an explicit grid in [1,148], got %d", peers->grid);
+      return -1;
+    }
+    grid = peers->grid;
+  }
+  param_kernel<kUpdate><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(vt, w, ema, pi, lo, hi, *hyper, state,
+                                                                            bump_global_step, 0);
+  TTD_CUDA(cudaGetLastError());
+  g_launch_count.fetch_add(1);
+  return 0;
+}

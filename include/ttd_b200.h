@@ -1,0 +1,146 @@
+/* C ABI of libttd_b200.so — the sm_100a kernel library of tensorflow_train_distributed_b200.
+ *
+ * Every function returns 0 on success; on failure it returns a non-zero code and
+ * ttd_last_error() describes what went wrong. Pointers are device pointers unless a
+ * parameter says "host". `stream` is a cudaStream_t passed as void*; all work is
+ * enqueued on it and nothing synchronises unless stated.
+ *
+ * Reference citations are to /root/reference/distribute_training.py (the TF1 script
+ * whose behaviour each kernel reproduces).
+ */
+#ifndef TTD_B200_H_
+#define TTD_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* ttd_last_error(void);
+/* library self-description: "ttd_b200 sm_100a <build stamp>" */
+const char* ttd_version(void);
+/* number of kernels launched by this library in this process since load (bench "gpu_launches") */
+uint64_t ttd_launch_count(void);
+
+/* ---- epilogue modes of the grouped tcgen05 GEMM ------------------------------------------ */
+enum {
+  TTD_EPI_FWD = 0,      /* out = dropout(act(acc + bias))            (reference :54-58) */
+  TTD_EPI_DGRAD = 1,    /* out = acc * dropout_mask/keep * act'(aux) (autodiff of :54-58) */
+  TTD_EPI_WGRAD = 2,    /* outf = scale * acc, fp32                  (autodiff of :54-55) */
+  TTD_EPI_FWD_XENT = 3  /* logits = acc + bias; mean sparse softmax CE + top-1 + dlogits (reference :77-82, :96, :125) */
+};
+enum { TTD_ACT_NONE = 0, TTD_ACT_RELU = 1, TTD_ACT_ELU = 2 };
+
+/* One GEMM problem D[M,N] = A[M,K] * B[N,K]^T. A and B are bf16, K contiguous ("K-major"),
+ * leading dimensions in elements and multiples of 8 (TMA needs 16-byte row pitch). */
+typedef struct TtdGemmDesc {
+  const void* a; int64_t lda;   /* bf16 [M, lda] */
+  const void* b; int64_t ldb;   /* bf16 [N, ldb] */
+  int32_t M, N, K;
+  int32_t block_n;              /* CTA tile width: multiple of 16 in [16, 256]; 0 = choose */
+  int32_t mode;                 /* TTD_EPI_* */
+  int32_t act;                  /* TTD_ACT_* (FWD: applied; DGRAD: derivative taken w.r.t. aux) */
+  float drop_rate;              /* dropout rate of the produced tensor (FWD) / of aux (DGRAD); 0 = off */
+  uint32_t layer_id;            /* stream id for the dropout RNG; FWD and its DGRAD must agree */
+  const float* bias;            /* fp32 [N] or NULL */
+  void* out; int64_t ldo;       /* bf16 [M, ldo] row-major result or NULL */
+  void* outT; int64_t ldt;      /* bf16 [N, ldt] transposed result or NULL */
+  float* outf; int64_t ldf;     /* fp32 [M, ldf] result (WGRAD: required; FWD*: optional copy of pre-dropout output/logits) */
+  const void* aux; int64_t ldaux; /* DGRAD: bf16 [M, ldaux] saved (post-dropout) activation */
+  float scale;                  /* WGRAD / XENT gradient scale */
+  const int64_t* labels;        /* XENT: int64 [M] */
+  float* metrics;               /* XENT: float[2] accumulators: += mean loss, += top-1 accuracy */
+} TtdGemmDesc;
+
+/* Launch up to 4 independent GEMM problems in ONE kernel (grid = sum of their tiles).
+ * tcgen05.mma (cta_group::1, M=128) with TMEM accumulators, TMA-fed, warp-specialised.
+ * step_ptr: device uint64 local-step counter keyed into the dropout RNG (may be NULL if no dropout).
+ * flags bit0: programmatic dependent launch. */
+int ttd_gemm_group(const TtdGemmDesc* descs_host, int count, uint64_t seed, const uint64_t* step_ptr,
+                   uint32_t flags, void* stream);
+
+/* ---- stand-alone softmax cross-entropy (any class count) --------------------------------- */
+/* logits fp32 [B, ldl]; labels int64 [B]; writes dlogits bf16 [B, ldd] (and transposed [C, ldt] if
+ * non-NULL) = scale*(softmax - onehot)/B, and accumulates mean loss / accuracy into metrics[0..1].
+ * Reference :77-82 (loss), :96 and :125 (in_top_k accuracy). */
+int ttd_softmax_xent(const float* logits, int64_t ldl, const int64_t* labels, int32_t B, int32_t C,
+                     void* dlogits, int64_t ldd, void* dlogitsT, int64_t ldt, float scale, float* metrics,
+                     void* stream);
+
+/* ---- input staging ------------------------------------------------------------------------ */
+/* x fp32 [B, F] -> xb bf16 [B, ldx] and xT bf16 [F, ldt] (row F of xT is the caller's ones row).
+ * Reference :191, :224-226 (the fed batch). */
+int ttd_prep_input(const float* x, int32_t B, int32_t F, void* xb, int64_t ldx, void* xT, int64_t ldt,
+                   void* stream);
+
+/* ---- parameter store: variable table ------------------------------------------------------ */
+/* One entry per dense layer group: kernel [rows, cols] immediately followed by bias [cols] in the
+ * flat fp32 buffer (so the group is a [rows+1, cols] matrix). */
+typedef struct TtdVarDesc {
+  int64_t offset;       /* element offset of the group in the flat buffers */
+  int32_t rows, cols;   /* kernel shape [in, out] (TF layout, reference A.1) */
+  int32_t regularize;   /* 1: the kernel rows take the L1/L2 term (reference :55 — hidden layers only) */
+  int32_t reserved;
+  void* w_rm; int64_t ld_rm;  /* bf16 [rows+1, ld_rm] compute copy, TF layout (dgrad B operand) or NULL */
+  void* w_t;  int64_t ld_t;   /* bf16 [cols, ld_t]   transposed compute copy (fwd B operand) or NULL */
+} TtdVarDesc;
+
+typedef struct TtdHyper {
+  float lr0;            /* INITIAL_LEARNING_RATE (:14) */
+  float decay_rate;     /* LEARNING_RATE_DECAY_FACTOR (:13) */
+  int64_t decay_steps;  /* int(60000 / BATCH_SIZE) (:120-122) */
+  int32_t staircase;    /* :140 */
+  int32_t reg_kind;     /* 0 none, 1 L1, 2 L2 */
+  float reg_scale;      /* :39 regularizer_scale */
+  float ema_decay;      /* MOVING_AVERAGE_DECAY (:12); <=0 disables the shadow update */
+  int32_t ema_warmup;   /* 1: min(decay, (1+n)/(10+n)) because num_updates=global_step (:156) */
+  float grad_scale;     /* multiplies the summed gradient (1/replicas_to_aggregate for the sync mean) */
+} TtdHyper;
+
+/* He / variance-scaling init (reference :49, A.5): truncated normal, sigma = sqrt(1.3*2/fan_in),
+ * bias row zero; also fills ema (if non-NULL) with the same values and refreshes the bf16 copies. */
+int ttd_init_params(float* w, float* ema, const TtdVarDesc* vars_host, int nvars, uint64_t seed, void* stream);
+
+/* Device-resident step state (one per process, 64 bytes). The host reads it only at log cadence. */
+typedef struct TtdStepState {
+  int64_t global_step;     /* shared step counter (reference :116); every sync replica keeps an identical copy */
+  uint64_t local_step;     /* this worker's step count (reference :217, :236); keys dropout RNG and barrier epochs */
+  float metrics_acc[2];    /* running (mean loss, accuracy) of the step in flight */
+  float metrics_out[2];    /* (loss, accuracy) of the last completed step (reference :225-226 fetches) */
+  uint32_t done_counter;   /* scratch: blocks finished in the current update launch */
+  float lr_last;           /* learning rate applied by the last update */
+  uint32_t reserved[6];
+} TtdStepState;
+
+#define TTD_MAX_PEERS 8
+/* Who contributes gradients and who receives the refreshed bf16 copies. Single GPU: n_grads =
+ * n_copies = 1, grads[0] = local gradient buffer, copy_delta[0] = 0, barrier = 0. */
+typedef struct TtdPeers {
+  const float* grads[TTD_MAX_PEERS];   /* flat gradient buffer of replica r (peer-mapped over NVLink) */
+  int64_t copy_delta[TTD_MAX_PEERS];   /* byte distance from a local bf16-copy address to replica r's */
+  uint32_t* flags[TTD_MAX_PEERS];      /* replica r's signal pad: u32[grid][TTD_MAX_PEERS], zero-initialised */
+  const float* grads_mc;               /* multicast (NVLS) mapping of the gradient buffers, or NULL */
+  int32_t n_grads, n_copies, rank;
+  int32_t barrier;                     /* 1: bracket the update with cross-replica barriers */
+  int32_t grid;                        /* barrier mode: CTA count, identical on all replicas, <= 148 */
+  int32_t reserved;
+} TtdPeers;
+
+/* Fused gradient push over the flat range [lo, hi) owned by the caller:
+ *   g = grad_scale * sum_r grads[r][i]  (+ L1/L2 term)   lr from state->global_step (staircase decay)
+ *   w -= lr*g ; ema -= (1-d)(ema-w) ; bf16 copies refreshed on every replica in `peers`
+ *   last CTA: ++global_step (if bump_global_step), ++local_step, metrics_out <- metrics_acc <- 0.
+ * Reference :136-140 (lr), :150-152 (apply + global_step), :153-161 (EMA), :50-55 (regulariser),
+ * :144-148 (SyncReplicasOptimizer mean-of-N aggregation when n_grads > 1). */
+int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars_host, int nvars, int64_t lo, int64_t hi,
+                     const TtdHyper* hyper_host, const TtdPeers* peers_host, TtdStepState* state,
+                     int32_t bump_global_step, void* stream);
+
+/* Rewrite only the bf16 compute copies from the fp32 master (after a restore). */
+int ttd_refresh_copies(const float* w, const TtdVarDesc* vars_host, int nvars, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TTD_B200_H_ */

@@ -1,0 +1,94 @@
+"""Python face of the grouped tcgen05 GEMM (``csrc/gemm_tcgen05.cu``).
+
+All matrices are bf16 with the reduction dimension contiguous ("K-major"), so a layer needs
+
+* forward   ``Z[B,out] = A[B,in] · Wt[out,in]^T``        (Wt = transposed compute copy)
+* dgrad     ``dA[B,in] = dZ[B,out] · W[in,out]^T``       (W = TF-layout compute copy)
+* wgrad     ``dW[in+1,out] = At[in+1,B] · dZt[out,B]^T``  (transposed activations; row ``in`` of At is
+  all ones, which makes row ``in`` of dW the bias gradient)
+
+which is why every epilogue can also emit the transposed copy of what it produces.
+Reference: forward_propagation / loss / minimize in distribute_training.py:39-63, :66-87, :152.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import torch
+
+from . import _native as N
+
+
+def _ld(t: torch.Tensor) -> int:
+    assert t.dim() == 2 and t.stride(1) == 1, "matrix must be 2-D with unit inner stride"
+    return t.stride(0)
+
+
+def make_desc(a: torch.Tensor, b: torch.Tensor, M: int, Nn: int, K: int, mode: int, *, act: int = N.ACT_NONE,
+              drop_rate: float = 0.0, layer_id: int = 0, bias: Optional[torch.Tensor] = None,
+              out: Optional[torch.Tensor] = None, outT: Optional[torch.Tensor] = None,
+              outf: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None, scale: float = 1.0,
+              labels: Optional[torch.Tensor] = None, metrics_ptr: Optional[int] = None,
+              block_n: int = 0) -> N.GemmDesc:
+    """Describe one GEMM problem. ``a`` is [>=M, lda] and ``b`` is [>=N, ldb] bf16 storage; M/N/K are the
+    logical extents (TMA zero-fills everything outside them)."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    d = N.GemmDesc()
+    d.a, d.lda = a.data_ptr(), _ld(a)
+    d.b, d.ldb = b.data_ptr(), _ld(b)
+    d.M, d.N, d.K = M, Nn, K
+    d.block_n = block_n
+    d.mode, d.act = mode, act
+    d.drop_rate, d.layer_id = float(drop_rate), layer_id
+    d.bias = N.ptr(bias)
+    if bias is not None:
+        assert bias.dtype == torch.float32
+    if out is not None:
+        assert out.dtype == torch.bfloat16
+        d.out, d.ldo = out.data_ptr(), _ld(out)
+    if outT is not None:
+        assert outT.dtype == torch.bfloat16
+        d.outT, d.ldt = outT.data_ptr(), _ld(outT)
+    if outf is not None:
+        assert outf.dtype == torch.float32
+        d.outf, d.ldf = outf.data_ptr(), _ld(outf)
+    if aux is not None:
+        assert aux.dtype == torch.bfloat16
+        d.aux, d.ldaux = aux.data_ptr(), _ld(aux)
+    d.scale = float(scale)
+    if labels is not None:
+        assert labels.dtype == torch.int64
+        d.labels = labels.data_ptr()
+    d.metrics = metrics_ptr
+    return d
+
+
+def gemm_group(descs: Sequence[N.GemmDesc], *, seed: int = 0, step_ptr: Optional[int] = None, pdl: bool = False,
+               stream: Optional[int] = None) -> None:
+    """Launch 1..4 problems as one kernel on the current stream."""
+    lib = N.load()
+    arr = (N.GemmDesc * len(descs))(*descs)
+    rc = lib.ttd_gemm_group(arr, len(descs), C.c_uint64(seed & (2**64 - 1)), step_ptr, 1 if pdl else 0,
+                            stream if stream is not None else N.cur_stream())
+    N.check(rc, "ttd_gemm_group")
+
+
+def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, C_: int, dlogits: Optional[torch.Tensor],
+                 dlogitsT: Optional[torch.Tensor], metrics: torch.Tensor, scale: float = 1.0) -> None:
+    lib = N.load()
+    B = labels.numel()
+    rc = lib.ttd_softmax_xent(logits.data_ptr(), _ld(logits), labels.data_ptr(), B, C_,
+                              N.ptr(dlogits), _ld(dlogits) if dlogits is not None else 0,
+                              N.ptr(dlogitsT), _ld(dlogitsT) if dlogitsT is not None else 0,
+                              float(scale), metrics.data_ptr(), N.cur_stream())
+    N.check(rc, "ttd_softmax_xent")
+
+
+def prep_input(x: torch.Tensor, xb: Optional[torch.Tensor], xT: Optional[torch.Tensor]) -> None:
+    lib = N.load()
+    B, F = x.shape
+    assert x.dtype == torch.float32 and x.is_contiguous()
+    rc = lib.ttd_prep_input(x.data_ptr(), B, F, N.ptr(xb), _ld(xb) if xb is not None else 0,
+                            N.ptr(xT), _ld(xT) if xT is not None else 0, N.cur_stream())
+    N.check(rc, "ttd_prep_input")
