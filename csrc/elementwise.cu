@@ -56,12 +56,27 @@ __global__ void __launch_bounds__(256) softmax_xent_kernel(const float* __restri
 
 // x fp32 [B,F] -> bf16 [B,ldx] and bf16 transposed [F,ldt]; 32x32 smem-tiled so both sides coalesce.
 // Reference: the feed of x-input (:191, :224-226).
+// With a device-resident dataset (pool_batches > 1) the batch is chosen on the device from the worker's
+// local step, so a captured graph walks through the pool without any host involvement; the labels of the
+// chosen batch are copied next to it (the xent epilogue reads a fixed address).
 __global__ void __launch_bounds__(256) prep_input_kernel(const float* __restrict__ x, int B, int F,
                                                          __nv_bfloat16* __restrict__ xb, long long ldx,
-                                                         __nv_bfloat16* __restrict__ xT, long long ldt) {
+                                                         __nv_bfloat16* __restrict__ xT, long long ldt,
+                                                         const long long* __restrict__ labels_pool,
+                                                         long long* __restrict__ labels_out, int pool_batches,
+                                                         const unsigned long long* __restrict__ step_ptr) {
   __shared__ float tile[32][33];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b0 = blockIdx.y * 32, f0 = blockIdx.x * 32;
+  if (pool_batches > 1 && step_ptr != nullptr) {
+    const unsigned long long slot = *step_ptr % static_cast<unsigned long long>(pool_batches);
+    x += slot * static_cast<unsigned long long>(B) * F;
+    if (labels_pool != nullptr) labels_pool += slot * static_cast<unsigned long long>(B);
+  }
+  if (labels_pool != nullptr && labels_out != nullptr && blockIdx.x == 0) {
+    const int b = b0 + threadIdx.x;
+    if (threadIdx.x < 32 && b < B) labels_out[b] = labels_pool[b];
+  }
 #pragma unroll
   for (int rr = 0; rr < 4; ++rr) {
     const int b = b0 + warp + 8 * rr, f = f0 + lane;
@@ -102,14 +117,17 @@ extern "C" int ttd_softmax_xent(const float* logits, int64_t ldl, const int64_t*
 }
 
 extern "C" int ttd_prep_input(const float* x, int32_t B, int32_t F, void* xb, int64_t ldx, void* xT, int64_t ldt,
-                              void* stream) {
+                              const int64_t* labels_pool, int64_t* labels_out, int32_t pool_batches,
+                              const uint64_t* step_ptr, void* stream) {
   if (B < 1 || F < 1) {
     set_error("ttd_prep_input: empty problem %dx%d", B, F);
     return -1;
   }
   dim3 grid((F + 31) / 32, (B + 31) / 32);
   prep_input_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      x, B, F, static_cast<__nv_bfloat16*>(xb), ldx, static_cast<__nv_bfloat16*>(xT), ldt);
+      x, B, F, static_cast<__nv_bfloat16*>(xb), ldx, static_cast<__nv_bfloat16*>(xT), ldt,
+      reinterpret_cast<const long long*>(labels_pool), reinterpret_cast<long long*>(labels_out), pool_batches,
+      reinterpret_cast<const unsigned long long*>(step_ptr));
   TTD_CUDA(cudaGetLastError());
   g_launch_count.fetch_add(1);
   return 0;

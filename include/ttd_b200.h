@@ -70,9 +70,12 @@ int ttd_softmax_xent(const float* logits, int64_t ldl, const int64_t* labels, in
 
 /* ---- input staging ------------------------------------------------------------------------ */
 /* x fp32 [B, F] -> xb bf16 [B, ldx] and xT bf16 [F, ldt] (row F of xT is the caller's ones row).
- * Reference :191, :224-226 (the fed batch). */
+ * Device-resident dataset: with pool_batches > 1, x is [pool_batches, B, F] and labels_pool is
+ * [pool_batches, B]; batch (*step_ptr % pool_batches) is staged and its labels copied to labels_out.
+ * Reference :191-192, :224-226 (the fed batch). */
 int ttd_prep_input(const float* x, int32_t B, int32_t F, void* xb, int64_t ldx, void* xT, int64_t ldt,
-                   void* stream);
+                   const int64_t* labels_pool, int64_t* labels_out, int32_t pool_batches,
+                   const uint64_t* step_ptr, void* stream);
 
 /* ---- parameter store: variable table ------------------------------------------------------ */
 /* One entry per dense layer group: kernel [rows, cols] immediately followed by bias [cols] in the

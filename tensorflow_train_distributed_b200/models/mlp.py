@@ -1,0 +1,117 @@
+"""The reference MLP (and its wide variant) as a fixed sequence of sm_100a kernel launches.
+
+Model of ``forward_propagation`` / ``loss`` / ``tower_loss`` (distribute_training.py:39-110):
+``[dense -> ELU -> dropout] x (L-1) -> dense`` -> mean sparse softmax cross-entropy + top-1 accuracy, with the
+backward pass that ``opt.minimize`` (:152) would have built. One training step is
+
+    prep_input                         fp32 batch -> bf16 + transposed bf16
+    L x   gemm(FWD)                    the last one is FWD_XENT: loss, accuracy and dlogits in its epilogue
+    L x   gemm(WGRAD [+ DGRAD])        one launch per layer, two problems per launch
+    apply_update                       the fused gradient push (parameter store)
+
+i.e. 2L + 2 launches (12 for the reference model), captured once into a CUDA graph by the trainer.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+
+from ..ops import _native as N
+from ..ops import gemm
+from ..parallel.param_store import GpuParamStore
+from ..parallel.sharding import LayerGroup, ParamLayout, mlp_groups
+
+
+def _pad8(n: int) -> int:
+    return -(-n // 8) * 8
+
+
+class GpuMlp:
+    def __init__(self, store: GpuParamStore, batch: int, *, activation: str = "elu", dropout_rate: float = 0.01,
+                 seed: int = 0, pdl: bool = False, keep_logits: bool = False):
+        self.store, self.B = store, batch
+        self.groups: List[LayerGroup] = store.layout.groups
+        self.L = len(self.groups)
+        self.act = N.ACT_CODES[activation]
+        self.drop = float(dropout_rate)
+        self.seed, self.pdl = seed, pdl
+        dev = store.device
+        B, ldB = batch, _pad8(batch)
+        sizes = [self.groups[0].rows] + [g.cols for g in self.groups]  # n_0 (input) .. n_L (classes)
+        self.sizes = sizes
+        bf = dict(device=dev, dtype=torch.bfloat16)
+        # static inputs
+        self.x = torch.zeros(B, sizes[0], device=dev, dtype=torch.float32)
+        self.labels = torch.zeros(B, device=dev, dtype=torch.int64)
+        # activations a_0..a_{L-1} (row-major, padded) and their transposes with the ones row for the bias grad
+        self.a = [torch.zeros(B, _pad8(sizes[l]), **bf) for l in range(self.L)]
+        self.aT = [torch.zeros(sizes[l] + 1, ldB, **bf) for l in range(self.L)]
+        for t, n in zip(self.aT, sizes):
+            t[n, :B] = 1.0
+        # dZ_1..dZ_L and transposes (index l-1)
+        self.dz = [torch.zeros(B, _pad8(sizes[l]), **bf) for l in range(1, self.L + 1)]
+        self.dzT = [torch.zeros(sizes[l], ldB, **bf) for l in range(1, self.L + 1)]
+        self.logits = torch.zeros(B, _pad8(sizes[-1]), device=dev, dtype=torch.float32) if keep_logits else None
+        self.x_pool: Optional[torch.Tensor] = None
+        self.labels_pool: Optional[torch.Tensor] = None
+        self._build_descs()
+
+    def set_device_dataset(self, x_pool: Optional[torch.Tensor], labels_pool: Optional[torch.Tensor]) -> None:
+        """Train from a device-resident pool [P, B, F] / [P, B]: batch ``local_step % P`` is picked on the
+        device, so a captured step graph needs no host feed. ``None`` returns to the fed batch."""
+        if x_pool is not None:
+            assert x_pool.dim() == 3 and tuple(x_pool.shape[1:]) == tuple(self.x.shape) and x_pool.is_contiguous()
+            assert labels_pool is not None and tuple(labels_pool.shape) == tuple(x_pool.shape[:2])
+        self.x_pool, self.labels_pool = x_pool, labels_pool
+
+    # -------------------------------------------------------------------------------------------
+    def _build_descs(self) -> None:
+        s, B, sz = self.store, self.B, self.sizes
+        self.fwd_descs, self.bwd_descs = [], []
+        for l in range(1, self.L + 1):
+            last = l == self.L
+            kw = dict(bias=s.bias(l - 1), layer_id=l)
+            if last:
+                d = gemm.make_desc(self.a[l - 1], s.w_t[l - 1], B, sz[l], sz[l - 1], N.EPI_FWD_XENT,
+                                   out=self.dz[l - 1], outT=self.dzT[l - 1], outf=self.logits, labels=self.labels,
+                                   metrics_ptr=s.metrics_acc_ptr, scale=1.0, **kw)
+            else:
+                d = gemm.make_desc(self.a[l - 1], s.w_t[l - 1], B, sz[l], sz[l - 1], N.EPI_FWD, act=self.act,
+                                   drop_rate=self.drop, out=self.a[l], outT=self.aT[l], **kw)
+            self.fwd_descs.append(d)
+        for l in range(self.L, 0, -1):
+            grp = [gemm.make_desc(self.aT[l - 1], self.dzT[l - 1], sz[l - 1] + 1, sz[l], B, N.EPI_WGRAD,
+                                  outf=s.grad_matrix(l - 1), scale=1.0)]
+            if l > 1:
+                grp.append(gemm.make_desc(self.dz[l - 1], s.w_rm[l - 1], B, sz[l - 1], sz[l], N.EPI_DGRAD, act=self.act,
+                                          drop_rate=self.drop, layer_id=l - 1, aux=self.a[l - 1],
+                                          out=self.dz[l - 2], outT=self.dzT[l - 2]))
+            self.bwd_descs.append(grp)
+
+    # -------------------------------------------------------------------------------------------
+    def launch_forward_backward(self) -> int:
+        """Enqueue forward + backward on the current stream; returns the number of kernels launched."""
+        step_ptr = self.store.local_step_ptr
+        if self.x_pool is not None:
+            gemm.prep_input(self.x_pool, self.a[0], self.aT[0], labels_pool=self.labels_pool, labels_out=self.labels,
+                            step_ptr=step_ptr)
+        else:
+            gemm.prep_input(self.x, self.a[0], self.aT[0])
+        n = 1
+        for d in self.fwd_descs:
+            gemm.gemm_group([d], seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
+            n += 1
+        for grp in self.bwd_descs:
+            gemm.gemm_group(grp, seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
+            n += 1
+        return n
+
+    def launch_step(self, bump_global_step: bool = True) -> int:
+        n = self.launch_forward_backward()
+        self.store.apply_update(bump_global_step)
+        return n + 1
+
+
+def build_layout(input_dim: int, layer_sizes: Sequence[int]) -> ParamLayout:
+    return ParamLayout(mlp_groups(input_dim, layer_sizes))

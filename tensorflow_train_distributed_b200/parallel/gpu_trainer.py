@@ -1,0 +1,199 @@
+"""GPU worker: owns a parameter-store shard, a model and the captured training step.
+
+In the reference a worker's step is ``mon_sess.run([train_op, loss, accuracy, global_step], feed_dict)``
+(distribute_training.py:224-226): ship the batch to the runtime, pull parameters from the ps over gRPC,
+compute, push gradients back, fetch three scalars. Here the same step is one CUDA-graph replay on the GPU that
+also owns 1/N of the parameters; the host copies the batch in, and reads the 64-byte state block back — per
+step on the end-to-end path, or only at log cadence (:229) when the caller does not need every value.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, Optional, Tuple
+
+import numpy as np
+import torch
+
+from ..config import TrainConfig
+from ..models import mlp as mlp_model
+from ..ops import _native as N
+from .param_store import GpuParamStore, Hyper
+from .sharding import ParamLayout
+
+
+@dataclass
+class StepValues:
+    """What the reference's ``mon_sess.run`` returns (:225): loss, accuracy, global_step."""
+    loss: float
+    accuracy: float
+    global_step: int
+    local_step: int
+    learning_rate: float
+
+
+def hyper_from_config(cfg: TrainConfig, n_replicas: int) -> Hyper:
+    return Hyper(lr0=cfg.initial_learning_rate, decay_rate=cfg.learning_rate_decay_factor,
+                 decay_steps=cfg.decay_steps, staircase=cfg.staircase, regularizer=cfg.regularizer,
+                 reg_scale=cfg.regularizer_scale,
+                 ema_decay=cfg.moving_average_decay if cfg.use_moving_average else 0.0, ema_warmup=True,
+                 grad_scale=1.0 / n_replicas)
+
+
+class GpuTrainer:
+    """One process per GPU. ``comm`` (a SymmetricComm) joins several of them into one parameter server."""
+
+    RING = 64  # pinned result slots for asynchronous per-step fetches
+
+    def __init__(self, cfg: TrainConfig, device_index: int = 0, comm=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("GpuTrainer needs a CUDA device; use the gloo transport on CPU-only machines")
+        self.cfg, self.comm = cfg, comm
+        self.device = torch.device("cuda", device_index)
+        torch.cuda.set_device(self.device)
+        self.world = comm.world_size if comm is not None else 1
+        self.rank = comm.rank if comm is not None else 0
+        self.sync = cfg.sync_replicas or self.world == 1
+        self.stream = torch.cuda.Stream(device=self.device)
+        self.layout: ParamLayout = self._build_layout()
+        n_agg = (cfg.replicas_to_aggregate or self.world) if self.sync else 1
+        self.hyper = hyper_from_config(cfg, n_agg)
+        with torch.cuda.stream(self.stream):
+            self.store = GpuParamStore(self.layout, self.hyper, self.device, comm=comm)
+            self.model = self._build_model()
+            self._pinned_state = torch.zeros(self.RING, 8, dtype=torch.int64).pin_memory()
+        self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self._launches_per_step = 0
+        self._slot = 0
+        self._steps_enqueued = 0
+        self._initialized = False
+
+    # -------------------------------------------------------------------------------------------
+    def _build_layout(self) -> ParamLayout:
+        cfg = self.cfg
+        if cfg.model in ("mlp", "wide_mlp"):
+            return mlp_model.build_layout(cfg.input_dim, cfg.layer_sizes)
+        if cfg.model == "lenet":
+            from ..models import lenet
+            return lenet.build_layout(cfg.num_classes)
+        raise ValueError(cfg.model)
+
+    def _build_model(self):
+        cfg = self.cfg
+        if cfg.model in ("mlp", "wide_mlp"):
+            return mlp_model.GpuMlp(self.store, cfg.batch_size, activation=cfg.activation,
+                                    dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank, pdl=cfg.pdl)
+        from ..models import lenet
+        return lenet.GpuLeNet(self.store, cfg.batch_size, activation=cfg.activation,
+                              dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank)
+
+    # -------------------------------------------------------------------------------------------
+    def initialize(self, restore: Optional[Dict[str, np.ndarray]] = None) -> None:
+        """Chief-init or restore (MonitoredTrainingSession bring-up, :209-215), then capture the step graph."""
+        with torch.cuda.stream(self.stream):
+            self.store.init(self.cfg.seed)
+            # one eager step warms every kernel (function attributes, tensor maps, module load) ...
+            self._launches_per_step = self.model.launch_step()
+            self.stream.synchronize()
+            if self.comm is not None:
+                self.comm.barrier()
+            # ... then the real initial state is laid down again
+            self.store.state.zero_()
+            if self.comm is None:
+                self.store.grads.zero_()
+            self.store.init(self.cfg.seed)
+            if restore is not None:
+                self.store.import_variables(restore)
+            self.stream.synchronize()
+            if self.comm is not None:
+                self.comm.reset_flags(self.store)
+                self.comm.barrier()
+        if self.cfg.cuda_graph:
+            self._capture()
+        self._initialized = True
+
+    def _capture(self) -> None:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=self.stream):
+            self.model.launch_step()
+        self._graph = g
+
+    def use_device_dataset(self, x_pool, labels_pool) -> None:
+        """Switch between a device-resident data set ([P,B,F] / [P,B], batch picked on the device from the
+        local step) and host-fed batches (``None``); the step graph is re-captured for the new source."""
+        self.stream.synchronize()
+        self.model.set_device_dataset(x_pool, labels_pool)
+        if self._graph is not None:
+            self._capture()
+
+    # -------------------------------------------------------------------------------------------
+    @property
+    def launches_per_step(self) -> int:
+        return self._launches_per_step
+
+    def load_batch(self, x, y) -> Tuple[int, int]:
+        """Host -> device copy of one batch on the trainer's stream; returns (bytes_x, bytes_y)."""
+        if isinstance(x, np.ndarray):
+            x = torch.from_numpy(x)
+        if isinstance(y, np.ndarray):
+            y = torch.from_numpy(y)
+        self.model.x.copy_(x.view(self.model.x.shape), non_blocking=True)
+        self.model.labels.copy_(y, non_blocking=True)
+        return x.numel() * x.element_size(), y.numel() * y.element_size()
+
+    def run_step(self) -> None:
+        """Enqueue one training step on the batch currently in the static input buffers."""
+        if self._graph is not None:
+            self._graph.replay()
+        else:
+            self.model.launch_step()
+        self._steps_enqueued += 1
+
+    def fetch_async(self) -> int:
+        """Enqueue a device -> host copy of the step state into the next pinned slot; returns the slot."""
+        slot = self._slot
+        self._pinned_state[slot].copy_(self.store.state, non_blocking=True)
+        self._slot = (slot + 1) % self.RING
+        return slot
+
+    def read_slot(self, slot: int) -> StepValues:
+        st = N.StepState.from_buffer_copy(self._pinned_state[slot].numpy().tobytes())
+        return StepValues(st.metrics_out[0], st.metrics_out[1], st.global_step, st.local_step, st.lr_last)
+
+    def train_step(self, x, y, fetch: bool = True) -> Optional[StepValues]:
+        """The user-facing step: feed one batch, run, and (optionally) fetch loss / accuracy / global_step."""
+        with torch.cuda.stream(self.stream):
+            self.load_batch(x, y)
+            self.run_step()
+            if not fetch:
+                return None
+            slot = self.fetch_async()
+        self.stream.synchronize()
+        return self.read_slot(slot)
+
+    def synchronize(self) -> None:
+        self.stream.synchronize()
+
+    def read_values(self) -> StepValues:
+        with torch.cuda.stream(self.stream):
+            slot = self.fetch_async()
+        self.stream.synchronize()
+        return self.read_slot(slot)
+
+    def global_step(self) -> int:
+        return self.read_values().global_step
+
+    # ---- checkpoint interface --------------------------------------------------------------------
+    def export_variables(self) -> Dict[str, np.ndarray]:
+        self.stream.synchronize()
+        if self.comm is not None:
+            self.comm.gather_master(self.store)
+        return self.store.export_variables()
+
+    def import_variables(self, tensors: Dict[str, np.ndarray]) -> None:
+        with torch.cuda.stream(self.stream):
+            self.store.import_variables(tensors)
+        self.stream.synchronize()
+
+    def close(self) -> None:
+        self.stream.synchronize()
+        self._graph = None

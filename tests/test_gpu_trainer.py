@@ -1,0 +1,139 @@
+"""End-to-end GPU step: gradients vs PyTorch autograd, graph vs eager, learning, checkpoint variables."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _cfg(**kw):
+    from tensorflow_train_distributed_b200.config import TrainConfig
+    base = dict(worker_hosts="127.0.0.1:2222", batch_size=128, save_checkpoint_secs=None, seed=11)
+    base.update(kw)
+    return TrainConfig(**base)
+
+
+def _torch_reference(vars_, x, y, sizes, act="elu"):
+    """fp32 PyTorch model with the SAME weights (TF layout [in,out])."""
+    ws, bs = [], []
+    names = [f"hidden{i + 1}" for i in range(len(sizes) - 1)] + ["output"]
+    h = x
+    for i, n in enumerate(names):
+        w = torch.tensor(vars_[n + "/kernel"], device="cuda", requires_grad=True)
+        b = torch.tensor(vars_[n + "/bias"], device="cuda", requires_grad=True)
+        ws.append(w), bs.append(b)
+        h = h @ w + b
+        if i < len(names) - 1:
+            h = torch.nn.functional.elu(h) if act == "elu" else torch.relu(h)
+    loss = torch.nn.functional.cross_entropy(h, y)
+    loss.backward()
+    return loss.item(), (h.argmax(1) == y).float().mean().item(), ws, bs
+
+
+@pytest.mark.parametrize("act", ["elu", "relu"])
+def test_step_gradients_match_autograd(act):
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    cfg = _cfg(dropout_rate=0.0, cuda_graph=False, activation=act)
+    tr = GpuTrainer(cfg)
+    tr.initialize()
+    ds = synthetic_mnist(1024, seed=5)
+    xs, ys = ds.next_batch(128)
+    vars_ = tr.export_variables()
+    with torch.cuda.stream(tr.stream):
+        tr.load_batch(xs, ys)
+        tr.store.state.view(torch.float32)[4:6] = 0
+        tr.model.launch_forward_backward()
+    tr.synchronize()
+    x, y = torch.tensor(xs, device="cuda"), torch.tensor(ys, device="cuda")
+    loss, acc, ws, bs = _torch_reference(vars_, x, y, cfg.layer_sizes, act)
+    st = tr.store.read_state()
+    assert abs(st.metrics_acc[0] - loss) < 2e-2 * max(1.0, loss)
+    assert abs(st.metrics_acc[1] - acc) <= 2.0 / 128
+    for i, (w, b) in enumerate(zip(ws, bs)):
+        gm = tr.store.grad_matrix(i)
+        scale = w.grad.abs().max().item()
+        assert torch.allclose(gm[:-1], w.grad, atol=5e-2 * scale), f"kernel grad of layer {i}"
+        assert torch.allclose(gm[-1], b.grad, atol=5e-2 * max(b.grad.abs().max().item(), 1e-6)), f"bias grad {i}"
+        cos = torch.nn.functional.cosine_similarity(gm[:-1].flatten(), w.grad.flatten(), dim=0).item()
+        assert cos > 0.995, (i, cos)
+    tr.close()
+
+
+def test_graph_replay_equals_eager_and_learns():
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    ds1, ds2 = synthetic_mnist(4096, seed=5), synthetic_mnist(4096, seed=5)
+    a = GpuTrainer(_cfg(cuda_graph=True))
+    b = GpuTrainer(_cfg(cuda_graph=False))
+    a.initialize(), b.initialize()
+    assert a.launches_per_step == 12  # prep + 5 fwd + 5 bwd + update for the reference model
+    la = lb = None
+    first = None
+    for _ in range(60):
+        xa, ya = ds1.next_batch(128)
+        xb, yb = ds2.next_batch(128)
+        la, lb = a.train_step(xa, ya), b.train_step(xb, yb)
+        first = first or la.loss
+    assert la.global_step == lb.global_step == 60 and la.local_step == 60
+    assert abs(la.loss - lb.loss) < 1e-5           # same kernels, same RNG stream: bitwise-equal up to atomics order
+    assert la.loss < 0.7 * first and la.accuracy > 0.5
+    va, vb = a.export_variables(), b.export_variables()
+    assert set(va) == set(vb) and len(va) == 21    # global_step + 10 variables + 10 EMA shadows
+    for k in va:
+        assert np.allclose(va[k], vb[k], atol=1e-5), k
+    assert va["hidden1/kernel"].shape == (784, 200) and va["global_step"] == 60
+    a.close(), b.close()
+
+
+def test_restore_roundtrip_continues_identically():
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    ds = synthetic_mnist(2048, seed=9)
+    a = GpuTrainer(_cfg(dropout_rate=0.0))
+    a.initialize()
+    batches = [ds.next_batch(128) for _ in range(12)]
+    for xs, ys in batches[:6]:
+        a.train_step(xs, ys)
+    snap = a.export_variables()
+    b = GpuTrainer(_cfg(dropout_rate=0.0, seed=999))
+    b.initialize(restore=snap)
+    assert b.global_step() == 6
+    for xs, ys in batches[6:]:
+        va, vb = a.train_step(xs, ys), b.train_step(xs, ys)
+    assert va.global_step == vb.global_step == 12
+    assert abs(va.loss - vb.loss) < 1e-5
+    a.close(), b.close()
+
+
+def test_device_resident_dataset_matches_fed_batches():
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    ds = synthetic_mnist(128 * 4, seed=2)
+    xs = torch.tensor(ds.images).view(4, 128, 784)
+    ys = torch.tensor(ds.labels).view(4, 128)
+    a, b = GpuTrainer(_cfg()), GpuTrainer(_cfg())
+    a.initialize(), b.initialize()
+    a.use_device_dataset(xs.cuda(), ys.cuda())
+    for i in range(10):
+        with torch.cuda.stream(a.stream):
+            a.run_step()
+        vb = b.train_step(xs[i % 4], ys[i % 4])
+    va = a.read_values()
+    assert va.global_step == vb.global_step == 10 and abs(va.loss - vb.loss) < 1e-5
+    a.close(), b.close()
+
+
+def test_wide_mlp_step_runs_and_learns():
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    tr = GpuTrainer(_cfg(model="wide_mlp", activation="relu", regularizer="none"))
+    tr.initialize()
+    ds = synthetic_mnist(2048, seed=4)
+    first = last = None
+    for _ in range(30):
+        xs, ys = ds.next_batch(128)
+        last = tr.train_step(xs, ys)
+        first = first or last.loss
+    assert last.loss < first and last.global_step == 30
+    tr.close()
