@@ -26,3 +26,21 @@ def pytest_collection_modifyitems(config, items):
             item.add_marker(skip_gpu)
         if "multigpu" in item.keywords and n < 2:
             item.add_marker(skip_multi)
+
+
+@pytest.fixture(autouse=True)
+def _seed_everything():
+    """Deterministic inputs: every test starts from the same torch / numpy RNG state."""
+    import random
+
+    import numpy as np
+    random.seed(0)
+    np.random.seed(0)
+    try:
+        import torch
+        torch.manual_seed(0)
+        if torch.cuda.is_available():
+            torch.cuda.manual_seed_all(0)
+    except Exception:  # noqa: BLE001
+        pass
+    yield

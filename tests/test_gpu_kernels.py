@@ -129,7 +129,8 @@ def test_fused_xent_matches_torch(ops, M, Nn, K):
     gemm.softmax_xent(logits, labels, Nn, dl2, None, m2)
     torch.cuda.synchronize()
     assert abs(m2[0].item() - loss.item()) < 1e-4 and abs(m2[1].item() - acc) < 1e-6
-    assert torch.equal(dl2, dl)
+    # different summation order (warp-parallel vs one thread per row): equal up to one bf16 ulp
+    assert torch.allclose(dl2.float(), dl.float(), rtol=1e-2, atol=1e-6)
 
 
 def test_grouped_launch_dgrad_plus_wgrad(ops):
