@@ -140,6 +140,20 @@ int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars_host, int nvar
                      const TtdHyper* hyper_host, const TtdPeers* peers_host, TtdStepState* state,
                      int32_t bump_global_step, void* stream);
 
+/* The same update for hosts that may not allocate device memory (no counterpart in the reference).
+ * Meant for callers embedded in a process that has given all of HBM to its own arena, or that cannot
+ * afford the device-wide synchronisation of cudaMalloc/cudaFree inside their loop. One gradient source,
+ * one GPU, no replica barriers. The kernel's completion counter and the variable table live in a 4 KiB
+ * array inside the library (resident on every GPU that loads it, until exit), so at most
+ * TTD_STATIC_MAX_VARS groups per call; more is refused with an error and nothing is launched.
+ * state->done_counter is not used. All calls on a GPU share that array: calls whose kernels could overlap
+ * on the GPU race and must be ordered by the caller. The first call on each GPU looks up the array's
+ * device address (cudaGetSymbolAddress); make it before any stream capture begins. */
+#define TTD_STATIC_MAX_VARS 64
+int ttd_apply_update_static(float* w, float* ema, const float* grad, const TtdVarDesc* vars_host, int nvars,
+                            int64_t lo, int64_t hi, const TtdHyper* hyper_host, TtdStepState* state,
+                            int32_t bump_global_step, void* stream);
+
 /* Rewrite only the bf16 compute copies from the fp32 master (after a restore). */
 int ttd_refresh_copies(const float* w, const TtdVarDesc* vars_host, int nvars, void* stream);
 
