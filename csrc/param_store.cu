@@ -180,6 +180,12 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
               ema[idx] = s - (1.0f - ema_d) * (s - val);
             }
           }
+          if (V.bias_c != nullptr && r == V.rows) {
+            for (int q = 0; q < pi.n_copies; ++q) {
+              float* dst = reinterpret_cast<float*>(reinterpret_cast<char*>(V.bias_c) + pi.copy_delta[q]);
+              dst[c] = val;
+            }
+          }
           if (V.w_rm != nullptr && r < V.rows) {
             const __nv_bfloat16 b = __float2bfloat16(val);
             for (int q = 0; q < pi.n_copies; ++q) {

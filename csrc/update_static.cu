@@ -9,15 +9,15 @@
 // variable table is limited to what fits in kernel parameters. Here both live in a fixed array inside
 // the library image, so the caller brings only its inputs and outputs.
 //
-// The scratch. `g_static_scratch` below is 4 KiB per GPU, resident from the moment the library is
+// The scratch. `g_static_scratch` below is 8 KiB per GPU, resident from the moment the library is
 // loaded on that GPU until the process exits:
 //     bytes    0..255   completion counter of the launch in flight (must be zero when a launch starts)
-//     bytes  256..3327  variable table, at most kStaticMaxVars (64) groups of 48 bytes
+//     bytes  256..4351  variable table, at most kStaticMaxVars (64) groups of 64 bytes
 // The limit is therefore 64 variable groups per call; a call with more is refused with an error text,
 // nothing is launched.
 //
 // Rules that follow from one shared array:
-//   * Every call on a GPU uses the same 4 KiB. The array keeps whatever the previous call left there,
+//   * Every call on a GPU uses the same 8 KiB. The array keeps whatever the previous call left there,
 //     so each call first clears the counter block on its stream and overwrites the table slots it uses.
 //   * Two calls whose kernels can be in flight on the same GPU at the same time (different streams, or
 //     different host threads) race on the counter and the table; callers must order them.
@@ -42,7 +42,7 @@ namespace {
 constexpr int kStaticMaxVars = TTD_STATIC_MAX_VARS;
 constexpr size_t kCounterBytes = 256;
 constexpr size_t kTableOffset = 256;
-constexpr size_t kScratchBytes = 4096;
+constexpr size_t kScratchBytes = 8192;
 static_assert(kTableOffset + kStaticMaxVars * sizeof(TtdVarDesc) <= kScratchBytes, "table must fit the scratch");
 
 // In host code this name is only a handle for cudaGetSymbolAddress; it is NOT a device address.
@@ -117,6 +117,7 @@ __global__ void __launch_bounds__(256) update_static_kernel(unsigned char* __res
         const float s = ema[idx];
         ema[idx] = s - (1.0f - ema_d) * (s - val);
       }
+      if (r == V.rows && V.bias_c != nullptr) V.bias_c[c] = val;
       if (r < V.rows) {
         const __nv_bfloat16 bv = __float2bfloat16(val);
         if (V.w_rm != nullptr) static_cast<__nv_bfloat16*>(V.w_rm)[static_cast<long long>(r) * V.ld_rm + c] = bv;
@@ -153,7 +154,7 @@ extern "C" int ttd_apply_update_static(float* w, float* ema, const float* grad, 
                                        TtdStepState* state, int32_t bump_global_step, void* stream) {
   if (nvars < 1 || nvars > kStaticMaxVars) {
     set_error("ttd_apply_update_static: %d variable groups requested but the built-in scratch holds at most %d "
-              "(4 KiB per GPU); split the call or use ttd_apply_update",
+              "(8 KiB per GPU); split the call or use ttd_apply_update",
               nvars, kStaticMaxVars);
     return -1;
   }

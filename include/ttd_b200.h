@@ -87,6 +87,7 @@ typedef struct TtdVarDesc {
   int32_t reserved;
   void* w_rm; int64_t ld_rm;  /* bf16 [rows+1, ld_rm] compute copy, TF layout (dgrad B operand) or NULL */
   void* w_t;  int64_t ld_t;   /* bf16 [cols, ld_t]   transposed compute copy (fwd B operand) or NULL */
+  float* bias_c;              /* fp32 [cols] compute copy of the bias (what the forward epilogue reads) or NULL */
 } TtdVarDesc;
 
 typedef struct TtdHyper {
@@ -143,7 +144,7 @@ int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars_host, int nvar
 /* The same update for hosts that may not allocate device memory (no counterpart in the reference).
  * Meant for callers embedded in a process that has given all of HBM to its own arena, or that cannot
  * afford the device-wide synchronisation of cudaMalloc/cudaFree inside their loop. One gradient source,
- * one GPU, no replica barriers. The kernel's completion counter and the variable table live in a 4 KiB
+ * one GPU, no replica barriers. The kernel's completion counter and the variable table live in a 8 KiB
  * array inside the library (resident on every GPU that loads it, until exit), so at most
  * TTD_STATIC_MAX_VARS groups per call; more is refused with an error and nothing is launched.
  * state->done_counter is not used. All calls on a GPU share that array: calls whose kernels could overlap

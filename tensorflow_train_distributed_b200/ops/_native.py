@@ -49,6 +49,7 @@ class VarDesc(C.Structure):
         ("regularize", C.c_int32), ("reserved", C.c_int32),
         ("w_rm", C.c_void_p), ("ld_rm", C.c_int64),
         ("w_t", C.c_void_p), ("ld_t", C.c_int64),
+        ("bias_c", C.c_void_p),
     ]
 
 

@@ -3,20 +3,24 @@
 What lives here replaces the ps job of the reference (``server.join()``, distribute_training.py:179-181, and
 the ``ApplyGradientDescent`` / ``AssignAdd(global_step)`` ops TF places on it, :150-152):
 
-* ``w``      flat fp32 master parameters, one ``[rows+1, cols]`` group per layer (kernel + bias)
+* ``w``      flat fp32 master parameters, one ``[rows+1, cols]`` group per layer (kernel + bias); a replica's
+             copy is authoritative only inside the range it owns
 * ``ema``    flat fp32 shadow variables (``<var>/ExponentialMovingAverage``)
-* ``grads``  flat fp32 gradient buffer — the wgrad GEMMs write straight into it; on several GPUs it lives in
-             symmetric memory so the owner of a range can read every replica's copy over NVLink
-* ``copies`` bf16 compute copies in the two K-major layouts the GEMMs need (``w_t`` for forward, ``w_rm``
-             for dgrad); refreshed by the update kernel on *every* replica (that is the parameter pull)
+* ``grads``  flat fp32 gradient buffer — the wgrad GEMMs write straight into it
+* ``copies`` compute copies refreshed by the update kernel on *every* replica (that is the parameter pull):
+             bf16 kernels in the two K-major layouts the GEMMs need (``w_t`` forward, ``w_rm`` dgrad) and the
+             fp32 biases the forward epilogues read
 * ``state``  64-byte device block: global_step, local_step, metric accumulators (never read by the host on the
              step path)
+
+With several GPUs, ``grads``, ``w``, the copies and a signal pad live in ONE symmetric (peer-mapped)
+allocation, so the address of anything on replica *r* is the local address plus one constant.
 """
 from __future__ import annotations
 
 import ctypes as C
 from dataclasses import dataclass
-from typing import Dict, List, Optional, Tuple
+from typing import Dict, List, Optional
 
 import numpy as np
 import torch
@@ -24,9 +28,15 @@ import torch
 from ..ops import _native as N
 from .sharding import EMA_SUFFIX, GLOBAL_STEP, FlatPlan, ParamLayout, flat
 
+FLAG_SLOTS = 148  # one signal row per CTA of a barrier-mode launch
+
 
 def _pad8(n: int) -> int:
     return -(-n // 8) * 8
+
+
+def _align(n: int, a: int) -> int:
+    return -(-n // a) * a
 
 
 @dataclass
@@ -57,54 +67,61 @@ class GpuParamStore:
         self.world = comm.world_size if comm is not None else 1
         self.rank = comm.rank if comm is not None else 0
         total = layout.total
-        self.w = torch.zeros(total, device=device, dtype=torch.float32)
-        self.ema = torch.zeros(total, device=device, dtype=torch.float32)
-        self.state = torch.zeros(8, device=device, dtype=torch.int64)  # TtdStepState (64 B)
 
-        # ---- bf16 compute copies: one arena, carved per layer -----------------------------------
+        # ---- carve one arena: grads | w | bf16 copies | fp32 bias copies | flags --------------------
         sizes = []
         for i, g in enumerate(layout.groups):
             want_rm = need_w_rm_first or i > 0  # dgrad of the first layer is never needed (input has no grad)
-            rm = g.rows * _pad8(g.cols) if want_rm else 0
-            t = g.cols * _pad8(g.rows)
-            sizes.append((rm, t))
-        arena_elems = sum(-(-a // 128) * 128 + -(-b // 128) * 128 for a, b in sizes)
-        grads_bytes = total * 4
-        copies_bytes = arena_elems * 2
+            sizes.append((g.rows * _pad8(g.cols) if want_rm else 0, g.cols * _pad8(g.rows), g.cols))
+        bf16_elems = sum(_align(a, 128) + _align(b, 128) for a, b, _ in sizes)
+        bias_elems = sum(_align(c, 64) for _, _, c in sizes)
+        o_grads = 0
+        o_w = o_grads + total * 4
+        o_bf16 = o_w + total * 4
+        o_bias = o_bf16 + _align(bf16_elems * 2, 256)
+        o_flags = o_bias + _align(bias_elems * 4, 256)
+        nbytes = o_flags + FLAG_SLOTS * N.MAX_PEERS * 4
         if comm is not None:
-            # grads | copies | flags   in one symmetric allocation, so peer addresses differ by one constant
-            self._flags_bytes = 148 * N.MAX_PEERS * 4
-            self._arena = comm.alloc(grads_bytes + copies_bytes + self._flags_bytes)
-            raw = self._arena.local  # uint8 tensor
-            raw.zero_()
-            self.grads = raw[:grads_bytes].view(torch.float32)
-            self.copies = raw[grads_bytes:grads_bytes + copies_bytes].view(torch.bfloat16)
-            self._flags_off = grads_bytes + copies_bytes
+            self._arena = comm.alloc(nbytes)
+            raw = self._arena.local
         else:
             self._arena = None
-            self.grads = torch.zeros(total, device=device, dtype=torch.float32)
-            self.copies = torch.zeros(arena_elems, device=device, dtype=torch.bfloat16)
+            raw = torch.empty(_align(nbytes, 4096), device=device, dtype=torch.uint8)
+        raw.zero_()
+        self._raw = raw
+        self._flags_off, self._flags_bytes = o_flags, FLAG_SLOTS * N.MAX_PEERS * 4
+        self.grads = raw[o_grads:o_grads + total * 4].view(torch.float32)
+        self.w = raw[o_w:o_w + total * 4].view(torch.float32)
+        copies = raw[o_bf16:o_bf16 + bf16_elems * 2].view(torch.bfloat16)
+        biases = raw[o_bias:o_bias + bias_elems * 4].view(torch.float32)
+        self.ema = torch.zeros(total, device=device, dtype=torch.float32)
+        self.state = torch.zeros(8, device=device, dtype=torch.int64)  # TtdStepState (64 B)
+
         self.w_rm: List[Optional[torch.Tensor]] = []
         self.w_t: List[torch.Tensor] = []
-        off = 0
-        for g, (rm, t) in zip(layout.groups, sizes):
+        self.bias_c: List[torch.Tensor] = []
+        off = boff = 0
+        for g, (rm, t, c) in zip(layout.groups, sizes):
             if rm:
-                self.w_rm.append(self.copies[off:off + rm].view(g.rows, _pad8(g.cols)))
-                off += -(-rm // 128) * 128
+                self.w_rm.append(copies[off:off + rm].view(g.rows, _pad8(g.cols)))
+                off += _align(rm, 128)
             else:
                 self.w_rm.append(None)
-            self.w_t.append(self.copies[off:off + t].view(g.cols, _pad8(g.rows)))
-            off += -(-t // 128) * 128
+            self.w_t.append(copies[off:off + t].view(g.cols, _pad8(g.rows)))
+            off += _align(t, 128)
+            self.bias_c.append(biases[boff:boff + c])
+            boff += _align(c, 64)
 
         # ---- variable table ----------------------------------------------------------------------
         descs = []
-        for g, rm, t in zip(layout.groups, self.w_rm, self.w_t):
+        for g, rm, t, b in zip(layout.groups, self.w_rm, self.w_t, self.bias_c):
             v = N.VarDesc()
             v.offset, v.rows, v.cols = g.offset, g.rows, g.cols
             v.regularize = 1 if g.regularize else 0
             if rm is not None:
                 v.w_rm, v.ld_rm = rm.data_ptr(), rm.stride(0)
             v.w_t, v.ld_t = t.data_ptr(), t.stride(0)
+            v.bias_c = b.data_ptr()
             descs.append(v)
         self.vars = (N.VarDesc * len(descs))(*descs)
         self.nvars = len(descs)
@@ -122,21 +139,28 @@ class GpuParamStore:
             return p
         base = self._arena.peer_ptrs
         for r in range(self.world):
-            p.grads[r] = base[r]
+            p.grads[r] = base[r]  # the arena starts with the gradient buffer
             p.copy_delta[r] = base[r] - base[self.rank]
             p.flags[r] = base[r] + self._flags_off
         p.grads_mc = None
         p.n_grads = p.n_copies = self.world
         p.rank = self.rank
         p.barrier = 1
-        p.grid = min(148, max(1, -(-(self.hi - self.lo) // (32 * 32 * 8))))
+        # identical on every replica (their CTAs meet pairwise): sized by the average owner range
+        per_owner = -(-self.layout.total // self.world)
+        p.grid = min(FLAG_SLOTS, max(1, -(-per_owner // (32 * 32 * 8))))
         return p
+
+    def peer_ptr(self, tensor: torch.Tensor, rank: int) -> int:
+        """Address of replica ``rank``'s counterpart of a tensor that lives in the symmetric arena."""
+        if self.comm is None:
+            return tensor.data_ptr()
+        return tensor.data_ptr() + (self._arena.peer_ptrs[rank] - self._arena.peer_ptrs[self.rank])
 
     # ---- views ---------------------------------------------------------------------------------
     def bias(self, i: int) -> torch.Tensor:
-        g = self.layout.groups[i]
-        o = g.offset + g.rows * g.cols
-        return self.w[o:o + g.cols]
+        """fp32 bias of layer ``i`` as the forward epilogue reads it (the pulled copy, not the master)."""
+        return self.bias_c[i]
 
     def grad_matrix(self, i: int) -> torch.Tensor:
         g = self.layout.groups[i]
@@ -171,6 +195,9 @@ class GpuParamStore:
         N.check(self.lib.ttd_apply_update(self.w.data_ptr(), ema_ptr, self.vars, self.nvars, self.lo, self.hi,
                                           C.byref(self._hyper_native), C.byref(self._peers), self.state_ptr,
                                           1 if bump_global_step else 0, N.cur_stream()), "ttd_apply_update")
+
+    def zero_flags(self) -> None:
+        self._raw[self._flags_off:self._flags_off + self._flags_bytes].zero_()
 
     # ---- host access (log cadence / checkpoints only) ---------------------------------------------
     def read_state(self) -> N.StepState:

@@ -67,8 +67,7 @@ class SymmetricComm:
 
     def reset_flags(self, store) -> None:
         """Zero this rank's signal pad (epochs restart with local_step = 0)."""
-        raw = store._arena.local
-        raw[store._flags_off:store._flags_off + store._flags_bytes].zero_()
+        store.zero_flags()
         torch.cuda.synchronize(self.device)
 
     def gather_master(self, store) -> None:
