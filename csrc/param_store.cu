@@ -146,52 +146,69 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
     if (t_hi <= lo || t_lo >= hi) continue;
 
     __syncthreads();  // previous tile's transposed reads are done
+    // phase 1: addresses + every load of this thread's four elements issued back to back, so the NVLink
+    // round trips to the peers' gradient buffers overlap instead of queueing behind one another
+    long long idxs[kTile / 8];
+    bool oks[kTile / 8];
+    float gsum[kTile / 8], wold[kTile / 8], sold[kTile / 8];
+#pragma unroll
+    for (int rr = 0; rr < kTile / 8; ++rr) {
+      const int r = r0 + warp + 8 * rr, c = c0 + lane;
+      const long long idx = V.offset + static_cast<long long>(r) * C + c;
+      const bool ok = r < R && c < C && idx >= lo && idx < hi;
+      idxs[rr] = idx;
+      oks[rr] = ok;
+      gsum[rr] = wold[rr] = sold[rr] = 0.0f;
+      if (MODE == kUpdate && ok) {
+        float g = 0.0f;
+#pragma unroll
+        for (int q = 0; q < kMaxPeers; ++q)
+          if (q < pi.n_grads) g += __ldcv(pi.grads[q] + idx);  // written by another GPU: never a stale L1 line
+        gsum[rr] = g;
+        wold[rr] = w[idx];
+        if (ema != nullptr && h.ema_decay > 0.0f) sold[rr] = ema[idx];
+      } else if (MODE == kRefresh && ok) {
+        wold[rr] = w[idx];
+      }
+    }
+    // phase 2: arithmetic + stores
 #pragma unroll
     for (int rr = 0; rr < kTile / 8; ++rr) {
       const int rl = warp + 8 * rr;
       const int r = r0 + rl, c = c0 + lane;
-      bool ok = false;
+      const bool ok = oks[rr];
+      const long long idx = idxs[rr];
       float val = 0.0f;
-      if (r < R && c < C) {
-        const long long idx = V.offset + static_cast<long long>(r) * C + c;
-        if (idx >= lo && idx < hi) {
-          ok = true;
-          if (MODE == kInit) {
-            val = (r < V.rows) ? trunc_normal(seed, static_cast<uint64_t>(idx)) * sqrtf(2.6f / static_cast<float>(V.rows))
-                               : 0.0f;
-            w[idx] = val;
-            if (ema) ema[idx] = val;
-          } else if (MODE == kRefresh) {
-            val = w[idx];
-          } else {
-            float g = 0.0f;
-#pragma unroll 1
-            for (int q = 0; q < pi.n_grads; ++q) g += pi.grads[q][idx];
-            g *= h.grad_scale;
-            const float wv = w[idx];
-            if (V.regularize && r < V.rows) {
-              if (h.reg_kind == 2) g += h.reg_scale * wv;
-              else if (h.reg_kind == 1) g += h.reg_scale * (wv > 0.0f ? 1.0f : (wv < 0.0f ? -1.0f : 0.0f));
-            }
-            val = wv - lr * g;
-            w[idx] = val;
-            if (ema != nullptr && h.ema_decay > 0.0f) {
-              const float s = ema[idx];
-              ema[idx] = s - (1.0f - ema_d) * (s - val);
-            }
+      if (ok) {
+        if (MODE == kInit) {
+          val = (r < V.rows) ? trunc_normal(seed, static_cast<uint64_t>(idx)) * sqrtf(2.6f / static_cast<float>(V.rows))
+                             : 0.0f;
+          w[idx] = val;
+          if (ema) ema[idx] = val;
+        } else if (MODE == kRefresh) {
+          val = wold[rr];
+        } else {
+          float g = gsum[rr] * h.grad_scale;
+          const float wv = wold[rr];
+          if (V.regularize && r < V.rows) {
+            if (h.reg_kind == 2) g += h.reg_scale * wv;
+            else if (h.reg_kind == 1) g += h.reg_scale * (wv > 0.0f ? 1.0f : (wv < 0.0f ? -1.0f : 0.0f));
           }
-          if (V.bias_c != nullptr && r == V.rows) {
-            for (int q = 0; q < pi.n_copies; ++q) {
-              float* dst = reinterpret_cast<float*>(reinterpret_cast<char*>(V.bias_c) + pi.copy_delta[q]);
-              dst[c] = val;
-            }
+          val = wv - lr * g;
+          w[idx] = val;
+          if (ema != nullptr && h.ema_decay > 0.0f) ema[idx] = sold[rr] - (1.0f - ema_d) * (sold[rr] - val);
+        }
+        if (V.bias_c != nullptr && r == V.rows) {
+          for (int q = 0; q < pi.n_copies; ++q) {
+            float* dst = reinterpret_cast<float*>(reinterpret_cast<char*>(V.bias_c) + pi.copy_delta[q]);
+            dst[c] = val;
           }
-          if (V.w_rm != nullptr && r < V.rows) {
-            const __nv_bfloat16 b = __float2bfloat16(val);
-            for (int q = 0; q < pi.n_copies; ++q) {
-              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(V.w_rm) + pi.copy_delta[q]);
-              dst[static_cast<long long>(r) * V.ld_rm + c] = b;
-            }
+        }
+        if (V.w_rm != nullptr && r < V.rows) {
+          const __nv_bfloat16 b = __float2bfloat16(val);
+          for (int q = 0; q < pi.n_copies; ++q) {
+            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(V.w_rm) + pi.copy_delta[q]);
+            dst[static_cast<long long>(r) * V.ld_rm + c] = b;
           }
         }
       }

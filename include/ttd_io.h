@@ -1,0 +1,54 @@
+/* C ABI of libttd_io.so — host-side I/O of tensorflow_train_distributed_b200 (no CUDA, no TensorFlow).
+ *
+ * Functions return 0 on success (or a non-NULL handle); on failure a non-zero code / NULL and
+ * ttdio_last_error() explains. Citations: /root/reference/distribute_training.py and SURVEY.md A.4.
+ */
+#ifndef TTD_IO_H_
+#define TTD_IO_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* ttdio_last_error(void);
+
+/* CRC-32C (Castagnoli); *_masked applies TensorFlow's rotate-and-add mask. */
+uint32_t ttdio_crc32c(const void* data, uint64_t n);
+uint32_t ttdio_crc32c_software(const void* data, uint64_t n); /* table path, for cross-checking the SSE4.2 path */
+uint32_t ttdio_crc32c_masked(const void* data, uint64_t n);
+
+/* TF DataType codes used in BundleEntryProto.dtype */
+enum { TTDIO_DT_FLOAT = 1, TTDIO_DT_DOUBLE = 2, TTDIO_DT_INT32 = 3, TTDIO_DT_UINT8 = 4, TTDIO_DT_INT64 = 9,
+       TTDIO_DT_BOOL = 10, TTDIO_DT_BFLOAT16 = 14, TTDIO_DT_HALF = 19 };
+
+/* ---- tensor bundle ("V2 checkpoint": what Saver writes for checkpoint_dir, reference :209-213) ---- */
+/* Phase 1 (every shard owner): write <prefix>.data-<shard>-of-<num> and a partial index under <prefix>_temp/. */
+int ttdio_bundle_write_shard(const char* prefix, int shard_id, int num_shards, int n_tensors,
+                             const char* const* names, const int32_t* dtypes, const int32_t* ndims,
+                             const int64_t* const* shapes, const void* const* data, const int64_t* nbytes);
+/* Phase 2 (chief): merge the partial indices into <prefix>.index (MergeV2Checkpoints). */
+int ttdio_bundle_merge(const char* prefix, int num_shards);
+
+void* ttdio_bundle_open(const char* prefix); /* parses and checksums <prefix>.index */
+void ttdio_bundle_close(void* reader);
+int ttdio_bundle_num_entries(void* reader);
+int ttdio_bundle_num_shards(void* reader);
+/* i-th entry in key order; shape8 must hold 8 values; name stays valid until close. */
+int ttdio_bundle_entry(void* reader, int i, const char** name, int32_t* dtype, int32_t* ndim, int64_t* shape8,
+                       int32_t* shard_id, int64_t* offset, int64_t* size, uint32_t* crc_masked);
+/* Reads one tensor's bytes (nbytes must equal its stored size) and verifies its checksum. */
+int ttdio_bundle_read(void* reader, const char* name, void* out, int64_t nbytes);
+
+/* ---- TensorBoard events (tf.summary.scalar, reference :128-132) ------------------------------- */
+void* ttdio_events_open(const char* logdir, double wall_time, const char* filename_suffix);
+const char* ttdio_events_path(void* writer);
+int ttdio_events_add_scalar(void* writer, const char* tag, float value, int64_t step, double wall_time);
+int ttdio_events_flush(void* writer);
+void ttdio_events_close(void* writer);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TTD_IO_H_ */

@@ -147,8 +147,9 @@ class GpuParamStore:
         p.rank = self.rank
         p.barrier = 1
         # identical on every replica (their CTAs meet pairwise): sized by the average owner range
+        # about one 32x32 tile per CTA: the update is latency-bound (NVLink round trips), so spread it wide
         per_owner = -(-self.layout.total // self.world)
-        p.grid = min(FLAG_SLOTS, max(1, -(-per_owner // (32 * 32 * 8))))
+        p.grid = min(FLAG_SLOTS, max(1, -(-per_owner // (32 * 32)) + 2 * self.nvars))
         return p
 
     def peer_ptr(self, tensor: torch.Tensor, rank: int) -> int:
