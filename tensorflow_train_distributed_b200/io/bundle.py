@@ -94,7 +94,7 @@ def write_shard(prefix: str, shard_id: int, num_shards: int, tensors: Mapping[st
     """Phase 1: write ``<prefix>.data-<shard_id>-of-<num_shards>`` and the partial index of this shard."""
     names = sorted(tensors)
     n = len(names)
-    arrs = [np.ascontiguousarray(tensors[k]) for k in names]
+    arrs = [np.asarray(tensors[k], order="C") for k in names]  # (ascontiguousarray would turn 0-d into 1-d)
     for k, a in zip(names, arrs):
         if a.dtype not in _NP_TO_DT:
             raise BundleError(f"{k}: dtype {a.dtype} has no TF DataType mapping")
