@@ -97,6 +97,7 @@ class TrainConfig:
     inject_fault: str = ""  # "step=N,rank=R" test hook (kill -> resume)
     rendezvous_timeout_secs: float = 120.0
     stop_grace_period_secs: float = 120.0
+    ps_idle_timeout_secs: float = 0.0  # >0: a ps exits after this long without worker traffic (reference: never, :181)
 
     # ------------------------------------------------------------------ derived values
     @property

@@ -1,0 +1,118 @@
+"""BASELINE config 1: real ps + worker processes on localhost over gloo (CPU tier, multi-process)."""
+import os
+import re
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_ports(n):
+    socks = [socket.socket() for _ in range(n)]
+    for s in socks:
+        s.bind(("127.0.0.1", 0))
+    ports = [s.getsockname()[1] for s in socks]
+    for s in socks:
+        s.close()
+    return ports
+
+
+def _launch(n_ps, n_workers, extra, ckpt_dir, timeout=240):
+    ports = _free_ports(n_ps + n_workers)
+    ps_hosts = ",".join(f"127.0.0.1:{p}" for p in ports[:n_ps])
+    w_hosts = ",".join(f"127.0.0.1:{p}" for p in ports[n_ps:])
+    base = [sys.executable, "-m", "tensorflow_train_distributed_b200.train", f"--ps_hosts={ps_hosts}",
+            f"--worker_hosts={w_hosts}", "--device=cpu", "--dataset_size=4096", f"--checkpoint_dir={ckpt_dir}",
+            "--log_every_n_steps=50"] + extra
+    env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="1", MKL_NUM_THREADS="1")
+    procs = []
+    for i in range(n_ps):
+        procs.append(("ps", i, subprocess.Popen(base + ["--job_name=ps", f"--task_id={i}"], env=env, cwd=ROOT,
+                                                stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    for i in range(n_workers):
+        procs.append(("worker", i, subprocess.Popen(base + ["--job_name=worker", f"--task_id={i}"], env=env, cwd=ROOT,
+                                                    stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    outs = {}
+    try:
+        for job, i, p in sorted(procs, key=lambda t: t[0] != "worker"):  # workers first: a ps outlives them
+            out, _ = p.communicate(timeout=timeout if job == "worker" else 30)
+            outs[(job, i)] = (p.returncode, out)
+    finally:
+        for _, _, p in procs:
+            if p.poll() is None:
+                p.kill()
+    return outs
+
+
+def _final(out):
+    m = re.search(r"total step: (\d+), global_step: (\d+)", out)
+    assert m, out[-2000:]
+    return int(m.group(1)), int(m.group(2))
+
+
+def _losses(out):
+    return [float(x) for x in re.findall(r"loss on training batch is ([0-9.e+-]+)", out)]
+
+
+@pytest.mark.timeout(300)
+def test_async_one_ps_two_workers(tmp_path):
+    """The reference's default topology (:26, :29): the 300 global steps are SHARED by the workers (:220-222)."""
+    d = str(tmp_path / "ck")
+    outs = _launch(1, 2, ["--training_steps=300", "--save_checkpoint_secs=2"], d)
+    for k, (rc, out) in outs.items():
+        assert rc == 0, (k, out[-3000:])
+    (s0, g0), (s1, g1) = _final(outs[("worker", 0)][1]), _final(outs[("worker", 1)][1])
+    assert g0 >= 300 and g1 >= 300
+    assert s0 + s1 >= 300 and s0 < 300 and s1 < 300  # shared global step: neither worker did all the steps
+    assert "session started" in outs[("worker", 0)][1]
+    l0 = _losses(outs[("worker", 0)][1])
+    assert l0 and l0[-1] < 1.0  # learned something from 2.30
+    from tensorflow_train_distributed_b200.io import bundle, checkpoint
+    prefix = checkpoint.latest_checkpoint(d)
+    assert prefix is not None
+    t = bundle.read_bundle(prefix)
+    assert int(t["global_step"]) >= 300 and t["hidden1/kernel"].shape == (784, 200)
+    assert len(t) == 21  # 11 reference entries + 10 EMA shadows
+    assert "applied" in outs[("ps", 0)][1]
+
+
+@pytest.mark.timeout(300)
+def test_sync_replicas_two_ps_two_workers(tmp_path):
+    """SyncReplicasOptimizer semantics (A.2): every worker runs ~last_step local steps, one global step per
+    aggregate, stale second gradient dropped, variables spread round-robin over two ps tasks."""
+    d = str(tmp_path / "ck")
+    outs = _launch(2, 2, ["--training_steps=120", "--sync_replicas", "--save_checkpoint_secs=none",
+                          "--save_checkpoint_steps=60", "--dropout_rate=0"], d)
+    for k, (rc, out) in outs.items():
+        assert rc == 0, (k, out[-3000:])
+    (s0, g0), (s1, g1) = _final(outs[("worker", 0)][1]), _final(outs[("worker", 1)][1])
+    assert g0 >= 120 and g1 >= 120
+    assert 120 <= s0 <= 125 and 120 <= s1 <= 125  # local steps run ~1 ahead of global steps
+    ps0 = outs[("ps", 0)][1]
+    m = re.search(r"'applied': (\d+), 'dropped_stale': (\d+)", ps0)
+    assert m and int(m.group(1)) >= 120 and int(m.group(2)) >= 1
+    from tensorflow_train_distributed_b200.io import bundle, checkpoint
+    r = bundle.BundleReader(checkpoint.latest_checkpoint(d))
+    assert r.num_shards == 2 and r.entries["global_step"]["shard_id"] == 0 and r.entries["hidden1/kernel"]["shard_id"] == 1
+
+
+@pytest.mark.timeout(400)
+def test_kill_and_resume_from_checkpoint(tmp_path):
+    """--inject_fault kills the chief mid-run; a relaunch on the same --checkpoint_dir resumes (:208)."""
+    d = str(tmp_path / "ck")
+    common = ["--training_steps=200", "--save_checkpoint_secs=none", "--save_checkpoint_steps=40"]
+    outs = _launch(1, 1, common + ["--inject_fault=step=90,rank=0", "--ps_idle_timeout_secs=3"], d, timeout=120)
+    assert "idle_timeout" in outs[("ps", 0)][1]  # the ps noticed that its only worker is gone
+    assert outs[("worker", 0)][0] != 0  # killed
+    from tensorflow_train_distributed_b200.io import checkpoint
+    mid = checkpoint.checkpoint_step(checkpoint.latest_checkpoint(d))
+    assert mid is not None and 40 <= mid < 200
+    outs = _launch(1, 1, common, d)
+    rc, out = outs[("worker", 0)]
+    assert rc == 0, out[-3000:]
+    steps, gs = _final(out)
+    assert gs >= 200 and steps <= 200 - mid + 2  # only the remaining steps were run
