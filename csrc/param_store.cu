@@ -47,9 +47,27 @@ struct PeerInfo {
   int n_copies;                      // replicas receiving the bf16 copies
   int rank;
   int barrier;                       // 1: run the cross-GPU barriers
+  // asynchronous (Hogwild) mode: every replica pulls from / pushes into the owners' masters directly
+  float* w_peer[kMaxPeers];          // fp32 master buffer of every replica (peer-mapped)
+  long long bounds[kMaxPeers + 1];   // owner k holds flat range [bounds[k], bounds[k+1])
+  TtdStepState* state0;              // step state of the owner of global_step (shard 0)
+  int n_owners;
 };
 
-enum { kInit = 0, kRefresh = 1, kUpdate = 2 };
+enum { kInit = 0, kRefresh = 1, kUpdate = 2, kAsyncPull = 3, kAsyncPush = 4 };
+
+__device__ __forceinline__ int owner_of(const PeerInfo& pi, long long idx) {
+  int o = 0;
+#pragma unroll
+  for (int k = 1; k < kMaxPeers; ++k)
+    if (k < pi.n_owners && idx >= pi.bounds[k]) o = k;
+  return o;
+}
+__device__ __forceinline__ long long ld_relaxed_sys_s64(const long long* p) {
+  long long v;
+  asm volatile("ld.relaxed.sys.global.s64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -113,9 +131,10 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  if (MODE == kUpdate) {
+  if (MODE == kUpdate || MODE == kAsyncPull || MODE == kAsyncPush) {
     if (threadIdx.x == 0) {
-      const long long gs = st->global_step;
+      // async: the one shared global_step lives with the owner of shard 0 and may move while we look at it
+      const long long gs = (MODE == kUpdate) ? st->global_step : ld_relaxed_sys_s64(reinterpret_cast<const long long*>(&pi.state0->global_step));
       double e = static_cast<double>(gs) / static_cast<double>(h.decay_steps);
       if (h.staircase) e = floor(e);
       s_lr = static_cast<float>(static_cast<double>(h.lr0) * pow(static_cast<double>(h.decay_rate), e));
@@ -126,7 +145,13 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
       s_lstep = st->local_step;
     }
     __syncthreads();
-    if (pi.barrier) replica_barrier(pi, static_cast<uint32_t>(2 * s_lstep + 1));
+    if (MODE == kUpdate && pi.barrier) replica_barrier(pi, static_cast<uint32_t>(2 * s_lstep + 1));
+  }
+  constexpr bool kAsync = (MODE == kAsyncPull || MODE == kAsyncPush);
+  const long long own_lo = lo, own_hi = hi;  // async kernels walk the whole buffer; [lo,hi) is what we own
+  if (kAsync) {
+    lo = 0;
+    hi = vt.v[vt.n - 1].offset + static_cast<long long>(vt.v[vt.n - 1].rows + 1) * vt.v[vt.n - 1].cols;
   }
   const float lr = s_lr, ema_d = s_ema_d;
 
@@ -169,6 +194,12 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
         if (ema != nullptr && h.ema_decay > 0.0f) sold[rr] = ema[idx];
       } else if (MODE == kRefresh && ok) {
         wold[rr] = w[idx];
+      } else if (MODE == kAsyncPull && ok) {
+        wold[rr] = __ldcv(pi.w_peer[owner_of(pi, idx)] + idx);  // M1: parameter pull straight from the owner
+        if (ema != nullptr && h.ema_decay > 0.0f && idx >= own_lo && idx < own_hi) sold[rr] = ema[idx];
+      } else if (MODE == kAsyncPush && ok) {
+        gsum[rr] = pi.grads[0][idx];
+        wold[rr] = w[idx];  // the snapshot this gradient was computed with
       }
     }
     // phase 2: arithmetic + stores
@@ -187,6 +218,22 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
           if (ema) ema[idx] = val;
         } else if (MODE == kRefresh) {
           val = wold[rr];
+        } else if (MODE == kAsyncPull) {
+          val = wold[rr];
+          if (idx >= own_lo && idx < own_hi) {  // owner pass: shadow variables follow the live master
+            if (ema != nullptr && h.ema_decay > 0.0f) ema[idx] = sold[rr] - (1.0f - ema_d) * (sold[rr] - val);
+          } else {
+            w[idx] = val;  // non-owned part of the local buffer = this step's fp32 snapshot
+          }
+        } else if (MODE == kAsyncPush) {
+          float g = gsum[rr] * h.grad_scale;
+          const float wv = wold[rr];
+          if (V.regularize && r < V.rows) {
+            if (h.reg_kind == 2) g += h.reg_scale * wv;
+            else if (h.reg_kind == 1) g += h.reg_scale * (wv > 0.0f ? 1.0f : (wv < 0.0f ? -1.0f : 0.0f));
+          }
+          // M2: unlocked apply on the owner (use_locking=False): one fire-and-forget NVLink atomic per element
+          atomicAdd_system(pi.w_peer[owner_of(pi, idx)] + idx, -lr * g);
         } else {
           float g = gsum[rr] * h.grad_scale;
           const float wv = wold[rr];
@@ -198,13 +245,13 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
           w[idx] = val;
           if (ema != nullptr && h.ema_decay > 0.0f) ema[idx] = sold[rr] - (1.0f - ema_d) * (sold[rr] - val);
         }
-        if (V.bias_c != nullptr && r == V.rows) {
+        if (MODE != kAsyncPush && V.bias_c != nullptr && r == V.rows) {
           for (int q = 0; q < pi.n_copies; ++q) {
             float* dst = reinterpret_cast<float*>(reinterpret_cast<char*>(V.bias_c) + pi.copy_delta[q]);
             dst[c] = val;
           }
         }
-        if (V.w_rm != nullptr && r < V.rows) {
+        if (MODE != kAsyncPush && V.w_rm != nullptr && r < V.rows) {
           const __nv_bfloat16 b = __float2bfloat16(val);
           for (int q = 0; q < pi.n_copies; ++q) {
             __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(V.w_rm) + pi.copy_delta[q]);
@@ -213,7 +260,7 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
         }
       }
       tile[rl][lane] = val;
-      tile_ok[rl][lane] = ok ? 1 : 0;
+      tile_ok[rl][lane] = (ok && MODE != kAsyncPush) ? 1 : 0;
     }
     if (V.w_t != nullptr) {
       __syncthreads();
@@ -232,8 +279,8 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
     }
   }
 
-  if (MODE == kUpdate) {
-    if (pi.barrier) {
+  if (MODE == kUpdate || MODE == kAsyncPush) {
+    if (MODE == kUpdate && pi.barrier) {
       __threadfence_system();
       replica_barrier(pi, static_cast<uint32_t>(2 * s_lstep + 2));
     }
@@ -245,7 +292,15 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
     __syncthreads();
     if (s_last && threadIdx.x == 0) {
       st->done_counter = 0;
-      if (bump_global_step) st->global_step += 1;
+      if (MODE == kAsyncPush) {
+        // AssignAdd(global_step) on the ps that holds it; keep a local mirror for the host's fetch
+        __threadfence_system();
+        const unsigned long long old =
+            atomicAdd_system(reinterpret_cast<unsigned long long*>(&pi.state0->global_step), 1ull);
+        if (pi.state0 != st) st->global_step = static_cast<long long>(old) + 1;
+      } else if (bump_global_step) {
+        st->global_step += 1;
+      }
       st->local_step += 1;
       st->lr_last = lr;
       st->metrics_out[0] = st->metrics_acc[0];
@@ -355,5 +410,58 @@ extern "C" int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars, in
                                                                             bump_global_step, 0);
   TTD_CUDA(cudaGetLastError());
   g_launch_count.fetch_add(1);
+  return 0;
+}
+
+static void fill_async(PeerInfo* pi, const TtdAsyncPeers* a, const float* local_grads) {
+  memset(pi, 0, sizeof(*pi));
+  for (int i = 0; i < kMaxPeers; ++i) pi->w_peer[i] = a->w_peer[i];
+  for (int i = 0; i <= kMaxPeers; ++i) pi->bounds[i] = a->bounds[i];
+  pi->state0 = a->state0;
+  pi->n_owners = a->n_owners;
+  pi->rank = a->rank;
+  pi->grads[0] = local_grads;
+  pi->n_grads = 1;
+  pi->n_copies = 1;
+}
+
+extern "C" int ttd_async_pull(float* w, float* ema, const TtdVarDesc* vars, int nvars, int64_t own_lo, int64_t own_hi,
+                              const TtdHyper* hyper, const TtdAsyncPeers* peers, TtdStepState* state, void* stream) {
+  VarTable vt;
+  int rc = build_table(&vt, vars, nvars);
+  if (rc) return rc;
+  if (peers == nullptr || peers->n_owners < 1 || peers->n_owners > kMaxPeers || peers->state0 == nullptr) {
+    set_error("ttd_async_pull: need 1..%d owners and the step state of owner 0", kMaxPeers);
+    return -1;
+  }
+  PeerInfo pi;
+  fill_async(&pi, peers, nullptr);
+  param_kernel<kAsyncPull><<<grid_for(vt.tile_begin[vt.n]), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      vt, w, ema, pi, own_lo, own_hi, *hyper, state, 0, 0);
+  TTD_CUDA(cudaGetLastError());
+  g_launch_count.fetch_add(1);
+  return 0;
+}
+
+extern "C" int ttd_async_push(float* w, const float* grads, const TtdVarDesc* vars, int nvars, const TtdHyper* hyper,
+                              const TtdAsyncPeers* peers, TtdStepState* state, void* stream) {
+  VarTable vt;
+  int rc = build_table(&vt, vars, nvars);
+  if (rc) return rc;
+  if (peers == nullptr || peers->n_owners < 1 || peers->n_owners > kMaxPeers || peers->state0 == nullptr) {
+    set_error("ttd_async_push: need 1..%d owners and the step state of owner 0", kMaxPeers);
+    return -1;
+  }
+  PeerInfo pi;
+  fill_async(&pi, peers, grads);
+  param_kernel<kAsyncPush><<<grid_for(vt.tile_begin[vt.n]), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      vt, w, nullptr, pi, 0, 0, *hyper, state, 1, 0);
+  TTD_CUDA(cudaGetLastError());
+  g_launch_count.fetch_add(1);
+  return 0;
+}
+
+extern "C" int ttd_copy_d2d(void* dst, const void* src, uint64_t nbytes, void* stream) {
+  TTD_CUDA(cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
   return 0;
 }

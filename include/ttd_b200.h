@@ -141,6 +141,27 @@ int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars_host, int nvar
                      const TtdHyper* hyper_host, const TtdPeers* peers_host, TtdStepState* state,
                      int32_t bump_global_step, void* stream);
 
+/* ---- asynchronous replicas (reference default: plain GradientDescentOptimizer, :149-152) ------------- */
+/* Hogwild on a GPU-sharded parameter server: no barrier, no aggregation. Each worker step is
+ *   ttd_async_pull   read every owner's fp32 master over NVLink -> local bf16/fp32 compute copies
+ *                    (+ the caller's own range: EMA shadow update)
+ *   forward / backward
+ *   ttd_async_push   w_owner[i] += -lr * (g[i] + reg)  as system-scope NVLink atomics (use_locking=False),
+ *                    then ONE atomic increment of the shared global_step held by owner 0. */
+typedef struct TtdAsyncPeers {
+  float* w_peer[TTD_MAX_PEERS];       /* fp32 master of replica r (peer-mapped) */
+  int64_t bounds[TTD_MAX_PEERS + 1];  /* owner k holds [bounds[k], bounds[k+1]) */
+  TtdStepState* state0;               /* owner 0's step state (peer-mapped): the shared global_step */
+  int32_t n_owners, rank;
+} TtdAsyncPeers;
+int ttd_async_pull(float* w, float* ema, const TtdVarDesc* vars_host, int nvars, int64_t own_lo, int64_t own_hi,
+                   const TtdHyper* hyper_host, const TtdAsyncPeers* peers_host, TtdStepState* state, void* stream);
+int ttd_async_push(float* w, const float* grads, const TtdVarDesc* vars_host, int nvars, const TtdHyper* hyper_host,
+                   const TtdAsyncPeers* peers_host, TtdStepState* state, void* stream);
+
+/* cudaMemcpyAsync(device -> device) on `stream`; lets Python snapshot peer-mapped shards for checkpoints. */
+int ttd_copy_d2d(void* dst, const void* src, uint64_t nbytes, void* stream);
+
 /* The same update for hosts that may not allocate device memory (no counterpart in the reference).
  * Meant for callers embedded in a process that has given all of HBM to its own arena, or that cannot
  * afford the device-wide synchronisation of cudaMalloc/cudaFree inside their loop. One gradient source,

@@ -107,10 +107,16 @@ class GpuMlp:
             n += 1
         return n
 
-    def launch_step(self, bump_global_step: bool = True) -> int:
+    def launch_step(self, bump_global_step: bool = True, sync: bool = True) -> int:
+        """sync: fwd/bwd + the fused push (aggregate of all replicas). async: pull + fwd/bwd + atomic push."""
+        if sync:
+            n = self.launch_forward_backward()
+            self.store.apply_update(bump_global_step)
+            return n + 1
+        self.store.async_pull()
         n = self.launch_forward_backward()
-        self.store.apply_update(bump_global_step)
-        return n + 1
+        self.store.async_push()
+        return n + 2
 
 
 def build_layout(input_dim: int, layer_sizes: Sequence[int]) -> ParamLayout:

@@ -102,6 +102,15 @@ class Peers(C.Structure):
     ]
 
 
+class AsyncPeers(C.Structure):
+    _fields_ = [
+        ("w_peer", C.c_void_p * MAX_PEERS),
+        ("bounds", C.c_int64 * (MAX_PEERS + 1)),
+        ("state0", C.c_void_p),
+        ("n_owners", C.c_int32), ("rank", C.c_int32),
+    ]
+
+
 class NativeError(RuntimeError):
     pass
 
@@ -146,6 +155,14 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.ttd_apply_update.restype = C.c_int
     lib.ttd_apply_update.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(VarDesc), C.c_int, C.c_int64, C.c_int64,
                                      C.POINTER(Hyper), C.POINTER(Peers), C.c_void_p, C.c_int32, C.c_void_p]
+    lib.ttd_async_pull.restype = C.c_int
+    lib.ttd_async_pull.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(VarDesc), C.c_int, C.c_int64, C.c_int64,
+                                   C.POINTER(Hyper), C.POINTER(AsyncPeers), C.c_void_p, C.c_void_p]
+    lib.ttd_async_push.restype = C.c_int
+    lib.ttd_async_push.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(VarDesc), C.c_int, C.POINTER(Hyper),
+                                   C.POINTER(AsyncPeers), C.c_void_p, C.c_void_p]
+    lib.ttd_copy_d2d.restype = C.c_int
+    lib.ttd_copy_d2d.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     _lib = lib
     return lib
 

@@ -92,7 +92,7 @@ class GpuTrainer:
         with torch.cuda.stream(self.stream):
             self.store.init(self.cfg.seed)
             # one eager step warms every kernel (function attributes, tensor maps, module load) ...
-            self._launches_per_step = self.model.launch_step()
+            self._launches_per_step = self.model.launch_step(sync=self.sync)
             self.stream.synchronize()
             if self.comm is not None:
                 self.comm.barrier()
@@ -114,7 +114,7 @@ class GpuTrainer:
     def _capture(self) -> None:
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, stream=self.stream):
-            self.model.launch_step()
+            self.model.launch_step(sync=self.sync)
         self._graph = g
 
     def use_device_dataset(self, x_pool, labels_pool) -> None:
@@ -145,7 +145,7 @@ class GpuTrainer:
         if self._graph is not None:
             self._graph.replay()
         else:
-            self.model.launch_step()
+            self.model.launch_step(sync=self.sync)
         self._steps_enqueued += 1
 
     def fetch_async(self) -> int:
@@ -184,9 +184,9 @@ class GpuTrainer:
 
     # ---- checkpoint interface --------------------------------------------------------------------
     def export_variables(self) -> Dict[str, np.ndarray]:
+        with torch.cuda.stream(self.stream):
+            self.store.snapshot_owner_shards()  # chief-side peer reads; no collective
         self.stream.synchronize()
-        if self.comm is not None:
-            self.comm.gather_master(self.store)
         return self.store.export_variables()
 
     def import_variables(self, tensors: Dict[str, np.ndarray]) -> None:

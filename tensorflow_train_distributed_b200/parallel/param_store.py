@@ -77,7 +77,9 @@ class GpuParamStore:
         bias_elems = sum(_align(c, 64) for _, _, c in sizes)
         o_grads = 0
         o_w = o_grads + total * 4
-        o_bf16 = o_w + total * 4
+        o_ema = o_w + total * 4
+        o_state = o_ema + total * 4
+        o_bf16 = o_state + 256
         o_bias = o_bf16 + _align(bf16_elems * 2, 256)
         o_flags = o_bias + _align(bias_elems * 4, 256)
         nbytes = o_flags + FLAG_SLOTS * N.MAX_PEERS * 4
@@ -94,8 +96,9 @@ class GpuParamStore:
         self.w = raw[o_w:o_w + total * 4].view(torch.float32)
         copies = raw[o_bf16:o_bf16 + bf16_elems * 2].view(torch.bfloat16)
         biases = raw[o_bias:o_bias + bias_elems * 4].view(torch.float32)
-        self.ema = torch.zeros(total, device=device, dtype=torch.float32)
-        self.state = torch.zeros(8, device=device, dtype=torch.int64)  # TtdStepState (64 B)
+        self.ema = raw[o_ema:o_ema + total * 4].view(torch.float32)
+        self.state = raw[o_state:o_state + 64].view(torch.int64)  # TtdStepState (64 B)
+        self._off = dict(grads=o_grads, w=o_w, ema=o_ema, state=o_state)
 
         self.w_rm: List[Optional[torch.Tensor]] = []
         self.w_t: List[torch.Tensor] = []
@@ -128,7 +131,10 @@ class GpuParamStore:
         self.plan: FlatPlan = flat(layout, self.world)
         self.lo, self.hi = self.plan.range_of(self.rank)
         self._peers = self._build_peers()
+        self._async_peers = self._build_async_peers()
         self._hyper_native = hyper.to_native()
+        h1 = Hyper(**{**hyper.__dict__, "grad_scale": 1.0})  # async: every gradient is applied on its own
+        self._hyper_async = h1.to_native()
 
     # ------------------------------------------------------------------------------------------
     def _build_peers(self) -> N.Peers:
@@ -151,6 +157,17 @@ class GpuParamStore:
         per_owner = -(-self.layout.total // self.world)
         p.grid = min(FLAG_SLOTS, max(1, -(-per_owner // (32 * 32)) + 2 * self.nvars))
         return p
+
+    def _build_async_peers(self) -> N.AsyncPeers:
+        a = N.AsyncPeers()
+        base = self._arena.peer_ptrs if self.comm is not None else [self._raw.data_ptr()]
+        for r in range(self.world):
+            a.w_peer[r] = base[r] + self._off["w"]
+        for k in range(self.world + 1):
+            a.bounds[k] = self.plan.bounds[k]
+        a.state0 = base[0] + self._off["state"]
+        a.n_owners, a.rank = self.world, self.rank
+        return a
 
     def peer_ptr(self, tensor: torch.Tensor, rank: int) -> int:
         """Address of replica ``rank``'s counterpart of a tensor that lives in the symmetric arena."""
@@ -196,6 +213,33 @@ class GpuParamStore:
         N.check(self.lib.ttd_apply_update(self.w.data_ptr(), ema_ptr, self.vars, self.nvars, self.lo, self.hi,
                                           C.byref(self._hyper_native), C.byref(self._peers), self.state_ptr,
                                           1 if bump_global_step else 0, N.cur_stream()), "ttd_apply_update")
+
+    def async_pull(self) -> None:
+        """M1 of the async step: fetch every owner's master over NVLink into the local compute copies."""
+        ema_ptr = self.ema.data_ptr() if self.hyper.ema_decay > 0 else None
+        N.check(self.lib.ttd_async_pull(self.w.data_ptr(), ema_ptr, self.vars, self.nvars, self.lo, self.hi,
+                                        C.byref(self._hyper_async), C.byref(self._async_peers), self.state_ptr,
+                                        N.cur_stream()), "ttd_async_pull")
+
+    def async_push(self) -> None:
+        """M2 of the async step: apply this worker's gradient to the owners with NVLink atomics, bump global_step."""
+        N.check(self.lib.ttd_async_push(self.w.data_ptr(), self.grads.data_ptr(), self.vars, self.nvars,
+                                        C.byref(self._hyper_async), C.byref(self._async_peers), self.state_ptr,
+                                        N.cur_stream()), "ttd_async_push")
+
+    def snapshot_owner_shards(self) -> None:
+        """Checkpoint path, ONE process: copy every owner's master / EMA range into the local buffers through the
+        peer mapping (no collective, so the chief's 60-second timer needs nobody's cooperation)."""
+        if self.comm is None:
+            return
+        base = self._arena.peer_ptrs
+        for owner in range(self.world):
+            lo, hi = self.plan.range_of(owner)
+            if owner == self.rank or hi <= lo:
+                continue
+            for key, t in (("w", self.w), ("ema", self.ema)):
+                src = base[owner] + self._off[key] + lo * 4
+                N.check(self.lib.ttd_copy_d2d(t.data_ptr() + lo * 4, src, (hi - lo) * 4, N.cur_stream()), "ttd_copy_d2d")
 
     def zero_flags(self) -> None:
         self._raw[self._flags_off:self._flags_off + self._flags_bytes].zero_()

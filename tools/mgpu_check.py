@@ -17,12 +17,83 @@ import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
 
+def async_check(comm) -> int:
+    """K2: Hogwild pushes. (a) atomic-sum exactness on integers-in-float, global_step counts every push;
+    (b) a short training run converges and the shared global_step equals steps x workers."""
+    from tensorflow_train_distributed_b200.config import TrainConfig
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    rank, world, B = comm.rank, comm.world_size, 128
+    hosts = ",".join(f"127.0.0.1:{2222 + i}" for i in range(world))
+    cfg = TrainConfig(worker_hosts=hosts, task_id=rank, batch_size=B, sync_replicas=False, save_checkpoint_secs=None,
+                      seed=5, initial_learning_rate=1.0, learning_rate_decay_factor=1.0, regularizer="none",
+                      use_moving_average=False, cuda_graph=False)
+    tr = GpuTrainer(cfg, device_index=comm.device.index, comm=comm)
+    tr.initialize()
+    st = tr.store
+    with torch.cuda.stream(tr.stream):
+        st.w.zero_()
+    tr.synchronize()
+    comm.barrier()
+    rounds = 3
+    for _ in range(rounds):
+        with torch.cuda.stream(tr.stream):
+            st.grads.fill_(float(rank + 1))
+            st.async_push()
+        tr.synchronize()
+    comm.barrier()
+    expect = -float(rounds * sum(r + 1 for r in range(world)))
+    own = st.w[st.lo:st.hi]
+    valid = torch.zeros(st.layout.total, dtype=torch.bool, device=own.device)
+    for g in st.layout.groups:
+        valid[g.offset:g.offset + g.numel] = True
+    exact = bool((own[valid[st.lo:st.hi]] == expect).all().item())
+    gs_after_pushes = tr.read_values().global_step if rank == 0 else 0
+    flag = torch.tensor([1 if exact else 0], device=comm.device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    tr.close()
+    comm.barrier()
+
+    steps = 60
+    cfg2 = TrainConfig(worker_hosts=hosts, task_id=rank, batch_size=B, sync_replicas=False, save_checkpoint_secs=None, seed=9)
+    tr2 = GpuTrainer(cfg2, device_index=comm.device.index, comm=comm)
+    tr2.initialize()
+    ds = synthetic_mnist(B * 64, seed=50 + rank)
+    first = last = None
+    for s in range(steps):
+        xs, ys = ds.next_batch(B)
+        last = tr2.train_step(xs, ys)
+        first = first if first is not None else last.loss
+    comm.barrier()
+    final = tr2.read_values()
+    gs0 = torch.tensor([final.global_step if rank == 0 else 0], device=comm.device)
+    dist.all_reduce(gs0, op=dist.ReduceOp.MAX)
+    vars_ = tr2.export_variables() if rank == 0 else None
+    ok = True
+    if rank == 0:
+        finite = all(np.isfinite(v).all() for v in vars_.values())
+        ok = bool(flag.item() == 1 and gs_after_pushes == rounds * world and int(gs0.item()) == steps * world
+                  and last.loss < 0.7 * first and finite)
+        print("MGPU " + json.dumps({"mode": "async", "world": world, "atomic_sum_exact": bool(flag.item() == 1),
+                                    "global_step_after_pushes": gs_after_pushes, "expected": rounds * world,
+                                    "global_step_after_training": int(gs0.item()), "expected_training": steps * world,
+                                    "first_loss": first, "last_loss": last.loss, "finite": finite, "ok": ok}), flush=True)
+    okt = torch.tensor([1 if ok else 0], device=comm.device)
+    dist.broadcast(okt, src=0)
+    tr2.close()
+    dist.barrier(device_ids=[comm.device.index])
+    dist.destroy_process_group()
+    return 0 if int(okt.item()) == 1 else 1
+
+
 def main() -> int:
     from tensorflow_train_distributed_b200.config import TrainConfig
     from tensorflow_train_distributed_b200.data import synthetic_mnist
     from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
     from tensorflow_train_distributed_b200.parallel.symmetric import SymmetricComm
     comm = SymmetricComm.from_env()
+    if os.environ.get("CHECK_MODE", "sync") == "async":
+        return async_check(comm)
     rank, world = comm.rank, comm.world_size
     steps, B = int(os.environ.get("CHECK_STEPS", "25")), 128
     model = os.environ.get("CHECK_MODEL", "mlp")
