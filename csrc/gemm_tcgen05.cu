@@ -54,6 +54,11 @@ struct GemmProblem {
 
 struct GemmGroup {
   GemmProblem p[kMaxProblems];
+  // Pull-fused B operand of problem 0 (the all-gather of the first layer's weights fused into its GEMM):
+  // k-block kb is fetched by TMA from the replica that owns it, through that replica's peer mapping.
+  CUtensorMap tma_b_peer[TTD_MAX_PEERS];
+  int kb_bound[TTD_MAX_PEERS + 1];  // owner o serves k-blocks [kb_bound[o], kb_bound[o+1])
+  int n_b_peers;                    // 0: problem 0 reads its B operand locally like every other problem
   int count;
   uint32_t seed_lo, seed_hi;
   const unsigned long long* step_ptr;
@@ -124,10 +129,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
   const int nbase = tile_n * P.block_n;
   const int num_kb = (P.K + kBlockK - 1) / kBlockK;
 
+  const bool pull_fused = (pi == 0 && g.n_b_peers > 0);
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&P.tma_a);
-    tma_prefetch_desc(&P.tma_b);
+    if (!pull_fused) tma_prefetch_desc(&P.tma_b);
   }
+  if (warp == 3 && pull_fused && lane < g.n_b_peers) tma_prefetch_desc(&g.tma_b_peer[lane]);
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < stages; ++s) {
       mbar_init(&full_bar[s], 1);
@@ -158,11 +165,17 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
       const uint32_t tx_bytes = kAStageBytes + P.block_n * kBlockK * 2;
       int s = 0;
       uint32_t ph = 0;
+      int owner = 0;
       for (int kb = 0; kb < num_kb; ++kb) {
+        const CUtensorMap* map_b = &P.tma_b;
+        if (pull_fused) {
+          while (owner + 1 < g.n_b_peers && kb >= g.kb_bound[owner + 1]) ++owner;
+          map_b = &g.tma_b_peer[owner];  // remote HBM over NVLink, same coordinates as the local copy
+        }
         mbar_wait(&empty_bar[s], ph ^ 1u);
         mbar_arrive_expect_tx(&full_bar[s], tx_bytes);
         tma_load_2d(sA + s * kAStageBytes, &P.tma_a, &full_bar[s], kb * kBlockK, m0);
-        tma_load_2d(sB + s * g.b_stage_bytes, &P.tma_b, &full_bar[s], kb * kBlockK, nbase);
+        tma_load_2d(sB + s * g.b_stage_bytes, map_b, &full_bar[s], kb * kBlockK, nbase);
         if (++s == stages) { s = 0; ph ^= 1u; }
       }
     }
@@ -443,6 +456,23 @@ extern "C" int ttd_gemm_group(const TtdGemmDesc* d, int count, uint64_t seed, co
     if (rc) return rc;
     rc = make_tmap(&P.tma_b, s.b, s.N, s.K, s.ldb, bn);
     if (rc) return rc;
+    if (i == 0 && s.n_b_peers > 0) {
+      if (s.n_b_peers > TTD_MAX_PEERS) {
+        set_error("ttd_gemm_group: at most %d B-operand peers", TTD_MAX_PEERS);
+        return -1;
+      }
+      g.n_b_peers = s.n_b_peers;
+      for (int o = 0; o < s.n_b_peers; ++o) {
+        if ((s.k_bound[o] % kBlockK != 0 && s.k_bound[o] != s.K) || s.k_bound[o + 1] < s.k_bound[o]) {
+          set_error("ttd_gemm_group: owner boundaries along K must be ascending multiples of %d (got %d)", kBlockK,
+                    s.k_bound[o]);
+          return -1;
+        }
+        rc = make_tmap(&g.tma_b_peer[o], s.b_peer[o], s.N, s.K, s.ldb, bn);
+        if (rc) return rc;
+      }
+      for (int o = 0; o <= s.n_b_peers; ++o) g.kb_bound[o] = (s.k_bound[o] + kBlockK - 1) / kBlockK;
+    }
     P.M = s.M; P.N = s.N; P.K = s.K;
     P.block_n = bn;
     P.tiles_m = (s.M + kBlockM - 1) / kBlockM;

@@ -271,6 +271,9 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
         if (tile_ok[lane][cl] && r < V.rows && c < C) {
           const __nv_bfloat16 b = __float2bfloat16(tile[lane][cl]);
           for (int q = 0; q < pi.n_copies; ++q) {
+            // flag bit0: consumers fetch this operand from its owner by TMA (pull-fused GEMM), so the
+            // transposed copy is NOT broadcast; only the owner's own buffer is refreshed
+            if ((V.reserved & 1) && pi.copy_delta[q] != 0) continue;
             __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(V.w_t) + pi.copy_delta[q]);
             dst[static_cast<long long>(c) * V.ld_t + r] = b;
           }

@@ -17,6 +17,8 @@
 extern "C" {
 #endif
 
+#define TTD_MAX_PEERS 8 /* replicas of one NVLink domain */
+
 const char* ttd_last_error(void);
 /* library self-description: "ttd_b200 sm_100a <build stamp>" */
 const char* ttd_version(void);
@@ -51,6 +53,13 @@ typedef struct TtdGemmDesc {
   float scale;                  /* WGRAD / XENT gradient scale */
   const int64_t* labels;        /* XENT: int64 [M] */
   float* metrics;               /* XENT: float[2] accumulators: += mean loss, += top-1 accuracy */
+  /* Pull-fused B operand (first problem of a group only): K is cut into owner ranges
+   * [k_bound[o], k_bound[o+1]) (multiples of 64); the tiles of range o are fetched by TMA from b_peer[o],
+   * replica o's peer-mapped copy of `b` (same shape and ld). This is the parameter pull of the first layer:
+   * an all-gather of W1 fused into the 784->hidden GEMM (reference M1 traffic, :186-190 placement). */
+  const void* b_peer[8];
+  int32_t k_bound[9];
+  int32_t n_b_peers;            /* 0 = B is read locally */
 } TtdGemmDesc;
 
 /* Launch up to 4 independent GEMM problems in ONE kernel (grid = sum of their tiles).
@@ -84,7 +93,7 @@ typedef struct TtdVarDesc {
   int64_t offset;       /* element offset of the group in the flat buffers */
   int32_t rows, cols;   /* kernel shape [in, out] (TF layout, reference A.1) */
   int32_t regularize;   /* 1: the kernel rows take the L1/L2 term (reference :55 — hidden layers only) */
-  int32_t reserved;
+  int32_t reserved;     /* flags; bit0: w_t is owner-local (read remotely by the pull-fused first GEMM), do not broadcast it */
   void* w_rm; int64_t ld_rm;  /* bf16 [rows+1, ld_rm] compute copy, TF layout (dgrad B operand) or NULL */
   void* w_t;  int64_t ld_t;   /* bf16 [cols, ld_t]   transposed compute copy (fwd B operand) or NULL */
   float* bias_c;              /* fp32 [cols] compute copy of the bias (what the forward epilogue reads) or NULL */
@@ -117,7 +126,6 @@ typedef struct TtdStepState {
   uint32_t reserved[6];
 } TtdStepState;
 
-#define TTD_MAX_PEERS 8
 /* Who contributes gradients and who receives the refreshed bf16 copies. Single GPU: n_grads =
  * n_copies = 1, grads[0] = local gradient buffer, copy_delta[0] = 0, barrier = 0. */
 typedef struct TtdPeers {

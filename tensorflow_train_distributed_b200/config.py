@@ -93,6 +93,7 @@ class TrainConfig:
     prefetch: int = 0  # >0: background reader threads (README "ReadByQueue" variant)
     cuda_graph: bool = True
     pdl: bool = False
+    pull_fused: bool = True  # sync multi-GPU: fetch W1 from its owners inside the first GEMM (K3) instead of broadcasting it
     write_events: bool = True
     inject_fault: str = ""  # "step=N,rank=R" test hook (kill -> resume)
     rendezvous_timeout_secs: float = 120.0

@@ -77,6 +77,9 @@ class GpuMlp:
                                    out=self.dz[l - 1], outT=self.dzT[l - 1], outf=self.logits, labels=self.labels,
                                    metrics_ptr=s.metrics_acc_ptr, scale=1.0, **kw)
             else:
+                if l == 1:
+                    ptrs, kb = s.first_layer_pull_plan()  # K3: all-gather of W1 fused into this GEMM
+                    kw.update(b_peers=ptrs, k_bounds=kb)
                 d = gemm.make_desc(self.a[l - 1], s.w_t[l - 1], B, sz[l], sz[l - 1], N.EPI_FWD, act=self.act,
                                    drop_rate=self.drop, out=self.a[l], outT=self.aT[l], **kw)
             self.fwd_descs.append(d)

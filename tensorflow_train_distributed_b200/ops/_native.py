@@ -39,6 +39,9 @@ class GemmDesc(C.Structure):
         ("scale", C.c_float),
         ("labels", C.c_void_p),
         ("metrics", C.c_void_p),
+        ("b_peer", C.c_void_p * 8),
+        ("k_bound", C.c_int32 * 9),
+        ("n_b_peers", C.c_int32),
     ]
 
 

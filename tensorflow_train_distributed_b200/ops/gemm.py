@@ -30,7 +30,8 @@ def make_desc(a: torch.Tensor, b: torch.Tensor, M: int, Nn: int, K: int, mode: i
               out: Optional[torch.Tensor] = None, outT: Optional[torch.Tensor] = None,
               outf: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None, scale: float = 1.0,
               labels: Optional[torch.Tensor] = None, metrics_ptr: Optional[int] = None,
-              block_n: int = 0) -> N.GemmDesc:
+              block_n: int = 0, b_peers: Optional[Sequence[int]] = None,
+              k_bounds: Optional[Sequence[int]] = None) -> N.GemmDesc:
     """Describe one GEMM problem. ``a`` is [>=M, lda] and ``b`` is [>=N, ldb] bf16 storage; M/N/K are the
     logical extents (TMA zero-fills everything outside them)."""
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
@@ -61,6 +62,14 @@ def make_desc(a: torch.Tensor, b: torch.Tensor, M: int, Nn: int, K: int, mode: i
         assert labels.dtype == torch.int64
         d.labels = labels.data_ptr()
     d.metrics = metrics_ptr
+    if b_peers:
+        # pull-fused B: k range o of the operand is read from replica o's peer-mapped copy (K3)
+        assert k_bounds is not None and len(k_bounds) == len(b_peers) + 1 and len(b_peers) <= N.MAX_PEERS
+        for o, ptr in enumerate(b_peers):
+            d.b_peer[o] = ptr
+        for o, kb in enumerate(k_bounds):
+            d.k_bound[o] = int(kb)
+        d.n_b_peers = len(b_peers)
     return d
 
 

@@ -58,7 +58,8 @@ class GpuTrainer:
         n_agg = (cfg.replicas_to_aggregate or self.world) if self.sync else 1
         self.hyper = hyper_from_config(cfg, n_agg)
         with torch.cuda.stream(self.stream):
-            self.store = GpuParamStore(self.layout, self.hyper, self.device, comm=comm)
+            self.store = GpuParamStore(self.layout, self.hyper, self.device, comm=comm,
+                                       pull_fused_first=self.sync and self.world > 1 and cfg.pull_fused)
             self.model = self._build_model()
             self._pinned_state = torch.zeros(self.RING, 8, dtype=torch.int64).pin_memory()
         self._graph: Optional[torch.cuda.CUDAGraph] = None

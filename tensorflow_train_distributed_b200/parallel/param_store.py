@@ -60,9 +60,12 @@ class Hyper:
 
 class GpuParamStore:
     def __init__(self, layout: ParamLayout, hyper: Hyper, device: torch.device, *, comm=None,
-                 need_w_rm_first: bool = False):
+                 need_w_rm_first: bool = False, pull_fused_first: bool = False):
         """``comm`` is a :class:`~.symmetric.SymmetricComm` for multi-GPU runs (None: single GPU)."""
         self.layout, self.hyper, self.device, self.comm = layout, hyper, device, comm
+        # K3: the first layer's transposed weights are not broadcast after an update; every replica's first
+        # GEMM fetches each k-block from its owner by TMA over NVLink instead
+        self.pull_fused_first = bool(pull_fused_first and comm is not None)
         self.lib = N.load()
         self.world = comm.world_size if comm is not None else 1
         self.rank = comm.rank if comm is not None else 0
@@ -125,6 +128,8 @@ class GpuParamStore:
                 v.w_rm, v.ld_rm = rm.data_ptr(), rm.stride(0)
             v.w_t, v.ld_t = t.data_ptr(), t.stride(0)
             v.bias_c = b.data_ptr()
+            if self.pull_fused_first and not descs:
+                v.reserved = 1
             descs.append(v)
         self.vars = (N.VarDesc * len(descs))(*descs)
         self.nvars = len(descs)
@@ -168,6 +173,17 @@ class GpuParamStore:
         a.state0 = base[0] + self._off["state"]
         a.n_owners, a.rank = self.world, self.rank
         return a
+
+    def first_layer_pull_plan(self):
+        """(peer addresses of w_t[0], K boundaries) for the pull-fused first GEMM, or (None, None)."""
+        if not self.pull_fused_first:
+            return None, None
+        g0 = self.layout.groups[0]
+        kb = [min(g0.rows, max(0, b - g0.offset) // g0.cols) for b in self.plan.bounds]
+        kb[-1] = g0.rows
+        # owners whose range lies past the first kernel serve nothing: their k range is empty
+        ptrs = [self.peer_ptr(self.w_t[0], r) for r in range(self.world)]
+        return ptrs, kb
 
     def peer_ptr(self, tensor: torch.Tensor, rank: int) -> int:
         """Address of replica ``rank``'s counterpart of a tensor that lives in the symmetric arena."""

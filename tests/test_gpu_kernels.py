@@ -251,3 +251,26 @@ def test_update_respects_owner_range(ops):
     torch.cuda.synchronize()
     changed = (s.w != w0)
     assert changed[1000:5000].all() and not changed[:1000].any() and not changed[5000:].any()
+
+
+def test_pull_fused_b_operand_reads_each_k_range_from_its_owner(ops):
+    """K3 on one GPU: every "replica" buffer holds valid data only in the K range it owns (NaN elsewhere);
+    the GEMM must stitch the B operand together from the right owners."""
+    N, gemm = ops
+    M, Nn, K = 128, 200, 784
+    a, b = _mk(M, K, scale=0.05, seed=21), _mk(Nn, K, seed=22)
+    bounds = [0, 128, 256, 320, 448, 576, 704, 784, 784]
+    peers = []
+    for o in range(8):
+        pb = torch.full_like(b, float("nan"))
+        pb[:, bounds[o]:bounds[o + 1]] = b[:, bounds[o]:bounds[o + 1]]
+        peers.append(pb)
+    poisoned_local = torch.full_like(b, float("nan"))
+    out = torch.zeros(M, 200, device="cuda")
+    d = gemm.make_desc(a, poisoned_local, M, Nn, K, N.EPI_FWD, outf=out, b_peers=[p.data_ptr() for p in peers],
+                       k_bounds=bounds)
+    gemm.gemm_group([d])
+    torch.cuda.synchronize()
+    ref = a[:, :K].float() @ b[:, :K].float().t()
+    assert torch.isfinite(out).all()
+    assert torch.allclose(out, ref, rtol=1e-4, atol=1e-3 * K ** 0.5)
