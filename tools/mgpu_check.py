@@ -110,7 +110,9 @@ def main() -> int:
         vals = tr.train_step(xs[rank * B:(rank + 1) * B], ys[rank * B:(rank + 1) * B])
     mine = tr.export_variables()  # gathers owner shards
     # replicas must hold bit-identical compute copies
-    digest = torch.stack([t.float().sum() for t in tr.store.w_t] + [b.sum() for b in tr.store.bias_c]).double()
+    # (w_t[0] is owner-local under K3 — the first GEMM pulls it from the owners — so it is not compared)
+    shared = tr.store.w_t[1:] + [t for t in tr.store.w_rm if t is not None]
+    digest = torch.stack([t.float().sum() for t in shared] + [b.sum() for b in tr.store.bias_c]).double()
     all_d = [torch.zeros_like(digest) for _ in range(world)]
     dist.all_gather(all_d, digest)
     same_copies = all(torch.equal(all_d[0], d) for d in all_d)
