@@ -85,12 +85,26 @@ __device__ __forceinline__ void replica_barrier(const PeerInfo& pi, uint32_t epo
   const int t = threadIdx.x;
   const int n = pi.n_grads;
   if (t < n) {
-    st_release_sys(pi.flags[t] + blockIdx.x * kMaxPeers + pi.rank, epoch);
+    // release: one system-scope fence (cumulative over everything the block wrote before the bar.sync),
+    // then a plain store of the epoch into the peer's pad. Polling uses relaxed loads — a fence per poll
+    // iteration would cost more than the NVLink hop it waits for — and a single fence acquires at the end.
+    __threadfence_system();
+    uint32_t* theirs = pi.flags[t] + blockIdx.x * kMaxPeers + pi.rank;
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(theirs), "r"(epoch) : "memory");
     const uint32_t* mine = pi.flags[pi.rank] + blockIdx.x * kMaxPeers + t;
-    const uint64_t t0 = globaltimer_ns();
-    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) {
-      if (globaltimer_ns() - t0 > 20000000000ull) __trap();  // a dead peer raises instead of hanging
+    uint32_t seen;
+    uint64_t t0 = 0;
+    uint32_t spins = 0;
+    while (true) {
+      asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
+      if (static_cast<int32_t>(seen - epoch) >= 0) break;
+      if ((++spins & 0x3FFu) == 0) {  // watchdog: a dead peer raises instead of hanging the GPU
+        const uint64_t now = globaltimer_ns();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > 20000000000ull) __trap();
+      }
     }
+    __threadfence_system();
   }
   __syncthreads();
 }
@@ -284,7 +298,6 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
 
   if (MODE == kUpdate || MODE == kAsyncPush) {
     if (MODE == kUpdate && pi.barrier) {
-      __threadfence_system();
       replica_barrier(pi, static_cast<uint32_t>(2 * s_lstep + 2));
     }
     // the last block to finish advances the step counters (nobody reads them any more in this launch)
