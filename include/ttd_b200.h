@@ -167,6 +167,12 @@ int ttd_async_pull(float* w, float* ema, const TtdVarDesc* vars_host, int nvars,
 int ttd_async_push(float* w, const float* grads, const TtdVarDesc* vars_host, int nvars, const TtdHyper* hyper_host,
                    const TtdAsyncPeers* peers_host, TtdStepState* state, void* stream);
 
+/* Diagnostic: two GPUs bounce a flag `iters` times through each other's memory (`mine` is polled,
+ * `theirs` is the peer mapping of the other side's flag); *out_ns = total device time. variant selects the
+ * ordering recipe: 0 volatile, 1 fence+relaxed, 2 release/acquire, 3 atomicExch, 4 red.release. */
+int ttd_diag_pingpong(uint32_t* mine, uint32_t* theirs, int rank, int iters, int variant,
+                      unsigned long long* out_ns, void* stream);
+
 /* cudaMemcpyAsync(device -> device) on `stream`; lets Python snapshot peer-mapped shards for checkpoints. */
 int ttd_copy_d2d(void* dst, const void* src, uint64_t nbytes, void* stream);
 
