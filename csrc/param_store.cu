@@ -148,6 +148,7 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
   __shared__ unsigned long long s_lstep;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint64_t k_start = (MODE == kUpdate && blockIdx.x == 0 && threadIdx.x == 0) ? globaltimer_ns() : 0;
 
   if (MODE == kUpdate || MODE == kAsyncPull || MODE == kAsyncPush) {
     if (threadIdx.x == 0) {
@@ -172,6 +173,12 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
     hi = vt.v[vt.n - 1].offset + static_cast<long long>(vt.v[vt.n - 1].rows + 1) * vt.v[vt.n - 1].cols;
   }
   const float lr = s_lr, ema_d = s_ema_d;
+  // phase clock of CTA 0 (ns since kernel start) for the push/pull trace: st->reserved[0..4] =
+  // {after barrier-in, after the gradient loads of its first tile, after its last tile, after barrier-out, #tiles}
+  const bool trace = (MODE == kUpdate) && blockIdx.x == 0 && threadIdx.x == 0;
+  const uint64_t k_t0 = k_start;
+  uint32_t tr_loads = 0, tr_ntiles = 0;
+  if (trace) st->reserved[0] = static_cast<uint32_t>(globaltimer_ns() - k_start);
 
   const int total_tiles = vt.tile_begin[vt.n];
   for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -219,6 +226,16 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
         gsum[rr] = pi.grads[0][idx];
         wold[rr] = w[idx];  // the snapshot this gradient was computed with
       }
+    }
+    if (trace) {
+      if (tr_ntiles == 0) {
+        float sink = 0.0f;
+#pragma unroll
+        for (int rr = 0; rr < kTile / 8; ++rr) sink += gsum[rr];
+        if (sink == 123.456f) st->reserved[5] = 1;  // forces the loads to have landed before the clock is read
+        tr_loads = static_cast<uint32_t>(globaltimer_ns() - k_t0);
+      }
+      ++tr_ntiles;
     }
     // phase 2: arithmetic + stores
 #pragma unroll
@@ -301,8 +318,15 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
   }
 
   if (MODE == kUpdate || MODE == kAsyncPush) {
+    const uint32_t tr_tiles_done = trace ? static_cast<uint32_t>(globaltimer_ns() - k_t0) : 0;
     if (MODE == kUpdate && pi.barrier) {
       replica_barrier<true>(pi, static_cast<uint32_t>(2 * s_lstep + 2));
+    }
+    if (trace) {
+      st->reserved[1] = tr_loads;
+      st->reserved[2] = tr_tiles_done;
+      st->reserved[3] = static_cast<uint32_t>(globaltimer_ns() - k_t0);
+      st->reserved[4] = tr_ntiles;
     }
     // the last block to finish advances the step counters (nobody reads them any more in this launch)
     __shared__ unsigned int s_last;

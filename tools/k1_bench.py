@@ -54,6 +54,9 @@ def main():
     res = {}
     lo, hi, ncopies, grid = st.lo, st.hi, st._peers.n_copies, st._peers.grid
     res.update([timeit("full")])
+    trace = st.state.cpu().view(torch.int32)[10:16].tolist()  # TtdStepState.reserved (phase clock of CTA 0, ns)
+    res["trace_ns"] = dict(after_barrier_in=trace[0], first_tile_loads=trace[1], tiles_done=trace[2],
+                           after_barrier_out=trace[3], tiles=trace[4])
 
     def no_bcast():
         st._peers.n_copies = 1
