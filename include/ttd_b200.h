@@ -173,6 +173,24 @@ int ttd_async_push(float* w, const float* grads, const TtdVarDesc* vars_host, in
 int ttd_diag_pingpong(uint32_t* mine, uint32_t* theirs, int rank, int iters, int variant,
                       unsigned long long* out_ns, void* stream);
 
+/* ---- LeNet-5 convolution stages (BASELINE config 5; the reference itself has no CNN) --------------------- */
+/* One stage = conv KHxKW stride 1 (SAME or VALID) + bias + activation + 2x2 max-pool, NHWC fp32 activations.
+ * Weights: bf16 [KH*KW*Cin, ldw] (the store's TF-layout compute copy of the HWIO kernel), bias fp32 [Cout]. */
+typedef struct TtdConvDesc {
+  int32_t B, H, W, Cin, Cout, KH, KW;
+  int32_t same_pad; /* 1: SAME (pad (K-1)/2), 0: VALID */
+} TtdConvDesc;
+/* pooled fp32 [B,PH,PW,Cout] (post-activation), argmax u8 (winning tap 0..3 of every pooled cell); optional
+ * bf16 flatten [B, ldflat] (+ transposed [PH*PW*Cout, ldflatT]) feeding the first dense layer's GEMM. */
+int ttd_conv_pool_fwd(const TtdConvDesc* d, const float* x, const void* w, int64_t ldw, const float* bias,
+                      int32_t act, float* pooled, uint8_t* argmax, void* flat, int64_t ldflat, void* flatT,
+                      int64_t ldflatT, void* stream);
+/* dzp = dL/d(pooled) * act'(pooled), fp32 or bf16 [B, ld_dzp]. Writes dw fp32 [KH*KW*Cin + 1, Cout] (last row =
+ * bias gradient) into the flat gradient buffer and, if dx != NULL, dx = dL/dx * act_below'(x_act) (fp32, shape of x). */
+int ttd_conv_pool_bwd(const TtdConvDesc* d, const void* dzp, int64_t ld_dzp, int32_t dzp_is_bf16,
+                      const uint8_t* argmax, const float* x, const void* w, int64_t ldw, float* dw, float* dx,
+                      const float* x_act, int32_t act_below, void* stream);
+
 /* cudaMemcpyAsync(device -> device) on `stream`; lets Python snapshot peer-mapped shards for checkpoints. */
 int ttd_copy_d2d(void* dst, const void* src, uint64_t nbytes, void* stream);
 

@@ -29,9 +29,15 @@ def _pad8(n: int) -> int:
 
 class GpuMlp:
     def __init__(self, store: GpuParamStore, batch: int, *, activation: str = "elu", dropout_rate: float = 0.01,
-                 seed: int = 0, pdl: bool = False, keep_logits: bool = False):
+                 seed: int = 0, pdl: bool = False, keep_logits: bool = False, first_group: int = 0,
+                 feed_input: bool = True, input_grad: bool = False):
+        """``first_group`` > 0 makes this the dense head of a larger model (LeNet): its input activations
+        ``a[0]`` / ``aT[0]`` are then written by the stage in front (``feed_input=False``) and, with
+        ``input_grad``, the backward pass also produces ``dz0`` = dL/d(input) * act'(input) for that stage."""
         self.store, self.B = store, batch
-        self.groups: List[LayerGroup] = store.layout.groups
+        self.g0 = first_group
+        self.feed_input, self.input_grad = feed_input, input_grad
+        self.groups: List[LayerGroup] = store.layout.groups[first_group:]
         self.L = len(self.groups)
         self.act = N.ACT_CODES[activation]
         self.drop = float(dropout_rate)
@@ -52,6 +58,7 @@ class GpuMlp:
         # dZ_1..dZ_L and transposes (index l-1)
         self.dz = [torch.zeros(B, _pad8(sizes[l]), **bf) for l in range(1, self.L + 1)]
         self.dzT = [torch.zeros(sizes[l], ldB, **bf) for l in range(1, self.L + 1)]
+        self.dz0 = torch.zeros(B, _pad8(sizes[0]), **bf) if input_grad else None
         self.logits = torch.zeros(B, _pad8(sizes[-1]), device=dev, dtype=torch.float32) if keep_logits else None
         self.x_pool: Optional[torch.Tensor] = None
         self.labels_pool: Optional[torch.Tensor] = None
@@ -67,44 +74,58 @@ class GpuMlp:
 
     # -------------------------------------------------------------------------------------------
     def _build_descs(self) -> None:
-        s, B, sz = self.store, self.B, self.sizes
+        s, B, sz, g0 = self.store, self.B, self.sizes, self.g0
         self.fwd_descs, self.bwd_descs = [], []
         for l in range(1, self.L + 1):
             last = l == self.L
-            kw = dict(bias=s.bias(l - 1), layer_id=l)
+            kw = dict(bias=s.bias(g0 + l - 1), layer_id=l)
             if last:
-                d = gemm.make_desc(self.a[l - 1], s.w_t[l - 1], B, sz[l], sz[l - 1], N.EPI_FWD_XENT,
+                d = gemm.make_desc(self.a[l - 1], s.w_t[g0 + l - 1], B, sz[l], sz[l - 1], N.EPI_FWD_XENT,
                                    out=self.dz[l - 1], outT=self.dzT[l - 1], outf=self.logits, labels=self.labels,
                                    metrics_ptr=s.metrics_acc_ptr, scale=1.0, **kw)
             else:
-                if l == 1:
+                if l == 1 and g0 == 0:
                     ptrs, kb = s.first_layer_pull_plan()  # K3: all-gather of W1 fused into this GEMM
                     kw.update(b_peers=ptrs, k_bounds=kb)
-                d = gemm.make_desc(self.a[l - 1], s.w_t[l - 1], B, sz[l], sz[l - 1], N.EPI_FWD, act=self.act,
+                d = gemm.make_desc(self.a[l - 1], s.w_t[g0 + l - 1], B, sz[l], sz[l - 1], N.EPI_FWD, act=self.act,
                                    drop_rate=self.drop, out=self.a[l], outT=self.aT[l], **kw)
             self.fwd_descs.append(d)
         for l in range(self.L, 0, -1):
             grp = [gemm.make_desc(self.aT[l - 1], self.dzT[l - 1], sz[l - 1] + 1, sz[l], B, N.EPI_WGRAD,
-                                  outf=s.grad_matrix(l - 1), scale=1.0)]
+                                  outf=s.grad_matrix(g0 + l - 1), scale=1.0)]
             if l > 1:
-                grp.append(gemm.make_desc(self.dz[l - 1], s.w_rm[l - 1], B, sz[l - 1], sz[l], N.EPI_DGRAD, act=self.act,
+                grp.append(gemm.make_desc(self.dz[l - 1], s.w_rm[g0 + l - 1], B, sz[l - 1], sz[l], N.EPI_DGRAD, act=self.act,
                                           drop_rate=self.drop, layer_id=l - 1, aux=self.a[l - 1],
                                           out=self.dz[l - 2], outT=self.dzT[l - 2]))
+            elif self.input_grad:  # gradient for the stage in front: times act'(its output), no dropout there
+                grp.append(gemm.make_desc(self.dz[0], s.w_rm[g0], B, sz[0], sz[1], N.EPI_DGRAD, act=self.act,
+                                          drop_rate=0.0, layer_id=0, aux=self.a[0], out=self.dz0))
             self.bwd_descs.append(grp)
 
     # -------------------------------------------------------------------------------------------
     def launch_forward_backward(self) -> int:
         """Enqueue forward + backward on the current stream; returns the number of kernels launched."""
         step_ptr = self.store.local_step_ptr
-        if self.x_pool is not None:
+        n = 0
+        if not self.feed_input:
+            pass
+        elif self.x_pool is not None:
             gemm.prep_input(self.x_pool, self.a[0], self.aT[0], labels_pool=self.labels_pool, labels_out=self.labels,
                             step_ptr=step_ptr)
         else:
             gemm.prep_input(self.x, self.a[0], self.aT[0])
-        n = 1
+        n += 1 if self.feed_input else 0
+        return n + self.launch_forward() + self.launch_backward()
+
+    def launch_forward(self) -> int:
+        step_ptr, n = self.store.local_step_ptr, 0
         for d in self.fwd_descs:
             gemm.gemm_group([d], seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
             n += 1
+        return n
+
+    def launch_backward(self) -> int:
+        step_ptr, n = self.store.local_step_ptr, 0
         for grp in self.bwd_descs:
             gemm.gemm_group(grp, seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
             n += 1

@@ -114,6 +114,11 @@ class AsyncPeers(C.Structure):
     ]
 
 
+class ConvDesc(C.Structure):
+    _fields_ = [("B", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("Cin", C.c_int32), ("Cout", C.c_int32),
+                ("KH", C.c_int32), ("KW", C.c_int32), ("same_pad", C.c_int32)]
+
+
 class NativeError(RuntimeError):
     pass
 
@@ -164,6 +169,12 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.ttd_async_push.restype = C.c_int
     lib.ttd_async_push.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(VarDesc), C.c_int, C.POINTER(Hyper),
                                    C.POINTER(AsyncPeers), C.c_void_p, C.c_void_p]
+    lib.ttd_conv_pool_fwd.restype = C.c_int
+    lib.ttd_conv_pool_fwd.argtypes = [C.POINTER(ConvDesc), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]
+    lib.ttd_conv_pool_bwd.restype = C.c_int
+    lib.ttd_conv_pool_bwd.argtypes = [C.POINTER(ConvDesc), C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
     lib.ttd_copy_d2d.restype = C.c_int
     lib.ttd_copy_d2d.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     _lib = lib

@@ -58,8 +58,9 @@ class GpuTrainer:
         n_agg = (cfg.replicas_to_aggregate or self.world) if self.sync else 1
         self.hyper = hyper_from_config(cfg, n_agg)
         with torch.cuda.stream(self.stream):
-            self.store = GpuParamStore(self.layout, self.hyper, self.device, comm=comm,
-                                       pull_fused_first=self.sync and self.world > 1 and cfg.pull_fused)
+            lenet = cfg.model == "lenet"
+            self.store = GpuParamStore(self.layout, self.hyper, self.device, comm=comm, need_w_rm_first=lenet,
+                                       pull_fused_first=self.sync and self.world > 1 and cfg.pull_fused and not lenet)
             self.model = self._build_model()
             self._pinned_state = torch.zeros(self.RING, 8, dtype=torch.int64).pin_memory()
         self._graph: Optional[torch.cuda.CUDAGraph] = None
@@ -85,7 +86,7 @@ class GpuTrainer:
                                     dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank, pdl=cfg.pdl)
         from ..models import lenet
         return lenet.GpuLeNet(self.store, cfg.batch_size, activation=cfg.activation,
-                              dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank)
+                              dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank, pdl=cfg.pdl)
 
     # -------------------------------------------------------------------------------------------
     def initialize(self, restore: Optional[Dict[str, np.ndarray]] = None) -> None:

@@ -137,3 +137,60 @@ def test_wide_mlp_step_runs_and_learns():
         first = first or last.loss
     assert last.loss < first and last.global_step == 30
     tr.close()
+
+
+def _lenet_reference(vars_, x, y, act="elu"):
+    """fp32 PyTorch LeNet with the same weights (HWIO kernels -> OIHW)."""
+    f = torch.nn.functional
+    p = {k: torch.tensor(v, device="cuda", requires_grad=True) for k, v in vars_.items()
+         if k != "global_step" and not k.endswith("ExponentialMovingAverage")}
+    a = f.elu if act == "elu" else torch.relu
+    h = x.view(-1, 1, 28, 28)
+    h = f.max_pool2d(a(f.conv2d(h, p["conv1/kernel"].permute(3, 2, 0, 1), p["conv1/bias"], padding=2)), 2)
+    h = f.max_pool2d(a(f.conv2d(h, p["conv2/kernel"].permute(3, 2, 0, 1), p["conv2/bias"])), 2)
+    h = h.permute(0, 2, 3, 1).reshape(x.shape[0], 400)  # TF flatten of NHWC
+    h = a(h @ p["fc1/kernel"] + p["fc1/bias"])
+    h = a(h @ p["fc2/kernel"] + p["fc2/bias"])
+    logits = h @ p["output/kernel"] + p["output/bias"]
+    loss = f.cross_entropy(logits, y)
+    loss.backward()
+    return loss.item(), p
+
+
+def test_lenet_gradients_match_autograd_and_it_learns():
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    cfg = _cfg(model="lenet", dropout_rate=0.0, cuda_graph=False)
+    tr = GpuTrainer(cfg)
+    tr.initialize()
+    vars_ = tr.export_variables()
+    assert vars_["conv1/kernel"].shape == (5, 5, 1, 6) and vars_["conv2/kernel"].shape == (5, 5, 6, 16)
+    assert sum(v.size for k, v in vars_.items() if k != "global_step" and "Exponential" not in k) == 61706
+    ds = synthetic_mnist(2048, seed=8)
+    xs, ys = ds.next_batch(128)
+    with torch.cuda.stream(tr.stream):
+        tr.load_batch(xs, ys)
+        tr.store.state.view(torch.float32)[4:6] = 0
+        tr.model.launch_forward_backward()
+    tr.synchronize()
+    loss, p = _lenet_reference(vars_, torch.tensor(xs, device="cuda"), torch.tensor(ys, device="cuda"))
+    st = tr.store.read_state()
+    assert abs(st.metrics_acc[0] - loss) < 3e-2 * max(1.0, loss)
+    names = ["conv1", "conv2", "fc1", "fc2", "output"]
+    for i, n in enumerate(names):
+        gm = tr.store.grad_matrix(i)
+        wg = p[n + "/kernel"].grad.reshape(gm.shape[0] - 1, gm.shape[1])
+        cos = torch.nn.functional.cosine_similarity(gm[:-1].flatten(), wg.flatten(), dim=0).item()
+        assert cos > 0.99, (n, cos)
+        assert torch.allclose(gm[:-1], wg, atol=6e-2 * wg.abs().max().item()), n
+        assert torch.allclose(gm[-1], p[n + "/bias"].grad, atol=6e-2 * max(p[n + "/bias"].grad.abs().max().item(), 1e-6)), n
+    tr.close()
+    tr = GpuTrainer(_cfg(model="lenet"))
+    tr.initialize()
+    first = last = None
+    for _ in range(80):
+        xs, ys = ds.next_batch(128)
+        last = tr.train_step(xs, ys)
+        first = first or last.loss
+    assert last.loss < 0.6 * first and last.global_step == 80
+    tr.close()
