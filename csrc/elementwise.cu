@@ -64,7 +64,8 @@ __global__ void __launch_bounds__(256) prep_input_kernel(const float* __restrict
                                                          __nv_bfloat16* __restrict__ xT, long long ldt,
                                                          const long long* __restrict__ labels_pool,
                                                          long long* __restrict__ labels_out, int pool_batches,
-                                                         const unsigned long long* __restrict__ step_ptr) {
+                                                         const unsigned long long* __restrict__ step_ptr,
+                                                         float* __restrict__ xf) {
   __shared__ float tile[32][33];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b0 = blockIdx.y * 32, f0 = blockIdx.x * 32;
@@ -84,6 +85,7 @@ __global__ void __launch_bounds__(256) prep_input_kernel(const float* __restrict
     if (b < B && f < F) {
       v = x[static_cast<long long>(b) * F + f];
       if (xb) xb[static_cast<long long>(b) * ldx + f] = __float2bfloat16(v);
+      if (xf) xf[static_cast<long long>(b) * F + f] = v;  // fp32 staging (conv front-ends read fp32 NHWC)
     }
     tile[warp + 8 * rr][lane] = v;
   }
@@ -118,7 +120,7 @@ extern "C" int ttd_softmax_xent(const float* logits, int64_t ldl, const int64_t*
 
 extern "C" int ttd_prep_input(const float* x, int32_t B, int32_t F, void* xb, int64_t ldx, void* xT, int64_t ldt,
                               const int64_t* labels_pool, int64_t* labels_out, int32_t pool_batches,
-                              const uint64_t* step_ptr, void* stream) {
+                              const uint64_t* step_ptr, float* xf, void* stream) {
   if (B < 1 || F < 1) {
     set_error("ttd_prep_input: empty problem %dx%d", B, F);
     return -1;
@@ -127,7 +129,7 @@ extern "C" int ttd_prep_input(const float* x, int32_t B, int32_t F, void* xb, in
   prep_input_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       x, B, F, static_cast<__nv_bfloat16*>(xb), ldx, static_cast<__nv_bfloat16*>(xT), ldt,
       reinterpret_cast<const long long*>(labels_pool), reinterpret_cast<long long*>(labels_out), pool_batches,
-      reinterpret_cast<const unsigned long long*>(step_ptr));
+      reinterpret_cast<const unsigned long long*>(step_ptr), xf);
   TTD_CUDA(cudaGetLastError());
   g_launch_count.fetch_add(1);
   return 0;

@@ -84,7 +84,7 @@ int ttd_softmax_xent(const float* logits, int64_t ldl, const int64_t* labels, in
  * Reference :191-192, :224-226 (the fed batch). */
 int ttd_prep_input(const float* x, int32_t B, int32_t F, void* xb, int64_t ldx, void* xT, int64_t ldt,
                    const int64_t* labels_pool, int64_t* labels_out, int32_t pool_batches,
-                   const uint64_t* step_ptr, void* stream);
+                   const uint64_t* step_ptr, float* xf /* optional fp32 copy [B, F] of the staged batch */, void* stream);
 
 /* ---- parameter store: variable table ------------------------------------------------------ */
 /* One entry per dense layer group: kernel [rows, cols] immediately followed by bias [cols] in the

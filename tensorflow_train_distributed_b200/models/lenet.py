@@ -73,13 +73,19 @@ class GpuLeNet:
         self.x_pool = self.labels_pool = None
 
     def set_device_dataset(self, x_pool, labels_pool) -> None:
-        if x_pool is not None:
-            raise NotImplementedError("the LeNet path is fed from the host (device-resident pools: MLP models)")
+        """Device-resident data set [P, B, 784] / [P, B]: the batch of ``local_step % P`` is staged on the device."""
+        self.x_pool, self.labels_pool = x_pool, labels_pool
 
     def launch_forward_backward(self) -> int:
+        from ..ops import gemm
+        extra = 0
+        if self.x_pool is not None:
+            gemm.prep_input(self.x_pool, None, None, labels_pool=self.labels_pool, labels_out=self.labels,
+                            step_ptr=self.store.local_step_ptr, xf=self.x)
+            extra = 1
         self.conv1.forward(self.x)
         self.conv2.forward(self.conv1.pooled, flat=self.head.a[0], flatT=self.head.aT[0])
-        n = 2 + self.head.launch_forward() + self.head.launch_backward()
+        n = 2 + extra + self.head.launch_forward() + self.head.launch_backward()
         n += self.conv2.backward(self.head.dz0, self.conv1.pooled, self.dpool1, self.act)
         n += self.conv1.backward(self.dpool1, self.x, None, N.ACT_NONE)
         return n

@@ -68,6 +68,7 @@ class GpuTrainer:
         self._slot = 0
         self._steps_enqueued = 0
         self._initialized = False
+        self._closed = False
 
     # -------------------------------------------------------------------------------------------
     def _build_layout(self) -> ParamLayout:
@@ -197,5 +198,9 @@ class GpuTrainer:
         self.stream.synchronize()
 
     def close(self) -> None:
+        """Peers keep reading / writing this process's memory until THEY are done: leave together."""
         self.stream.synchronize()
+        if self.comm is not None and not self._closed:
+            self.comm.barrier()
+        self._closed = True
         self._graph = None
