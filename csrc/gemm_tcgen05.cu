@@ -66,6 +66,7 @@ struct GemmGroup {
   int b_stage_bytes;
   int tmem_cols;
   int use_pdl;
+  int cluster;  // >1: CTAs of a cluster own consecutive N tiles of one M tile and share the A tile by TMA multicast
 };
 
 __device__ __forceinline__ void store_bf16x8(__nv_bfloat16* dst, const float* v) {
@@ -123,8 +124,13 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
     if (i < g.count && static_cast<int>(blockIdx.x) >= g.p[i].tile_begin) pi = i;
   const GemmProblem& P = g.p[pi];
   const int tile = blockIdx.x - P.tile_begin;
-  const int tile_m = tile % P.tiles_m;
-  const int tile_n = tile / P.tiles_m;
+  const int cl = g.cluster;
+  uint32_t cta_rank = 0;
+  if (cl > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+  const uint16_t cl_mask = static_cast<uint16_t>((1u << cl) - 1u);
+  // cluster mode walks N fastest so that the CTAs of one cluster sit on the same rows of A
+  const int tile_m = cl > 1 ? tile / P.tiles_n : tile % P.tiles_m;
+  const int tile_n = cl > 1 ? tile % P.tiles_n : tile / P.tiles_m;
   const int m0 = tile_m * kBlockM;
   const int nbase = tile_n * P.block_n;
   const int num_kb = (P.K + kBlockK - 1) / kBlockK;
@@ -138,7 +144,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < stages; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
+      mbar_init(&empty_bar[s], static_cast<uint32_t>(cl));  // every CTA that received the multicast frees the slot
     }
     mbar_init(tmem_full_bar, 1);
     fence_mbar_init();
@@ -149,6 +155,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
   }
   tc_fence_before();
   __syncthreads();
+  if (cl > 1) {  // peers' barriers must exist before anyone multicasts into them
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  }
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -174,7 +184,15 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
         }
         mbar_wait(&empty_bar[s], ph ^ 1u);
         mbar_arrive_expect_tx(&full_bar[s], tx_bytes);
-        tma_load_2d(sA + s * kAStageBytes, &P.tma_a, &full_bar[s], kb * kBlockK, m0);
+        if (cl > 1) {
+          // this CTA fetches 1/cl of the A tile and the TMA unit delivers it to every CTA of the cluster:
+          // A crosses the L2->SM fabric once per cluster instead of once per CTA
+          const int rows = kBlockM / cl;
+          tma_load_2d_mcast(sA + s * kAStageBytes + cta_rank * rows * (kBlockK * 2), &P.tma_a, &full_bar[s],
+                            kb * kBlockK, m0 + static_cast<int>(cta_rank) * rows, cl_mask);
+        } else {
+          tma_load_2d(sA + s * kAStageBytes, &P.tma_a, &full_bar[s], kb * kBlockK, m0);
+        }
         tma_load_2d(sB + s * g.b_stage_bytes, map_b, &full_bar[s], kb * kBlockK, nbase);
         if (++s == stages) { s = 0; ph ^= 1u; }
       }
@@ -196,7 +214,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
           const uint64_t db = umma_desc_k_sw128(b_addr + k * 32);
           umma_bf16_ss(tmem_base, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
         }
-        umma_commit(&empty_bar[s]);  // smem slot reusable once these MMAs have drained
+        if (cl > 1) umma_commit_mcast(&empty_bar[s], cl_mask);  // tell every producer that feeds this slot
+        else umma_commit(&empty_bar[s]);                       // smem slot reusable once these MMAs have drained
         if (++s == stages) { s = 0; ph ^= 1u; }
       }
       umma_commit(tmem_full_bar);  // accumulator complete
@@ -275,13 +294,40 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
     } else {
       const float keep = 1.0f - P.drop_rate;
       const float inv_keep = 1.0f / keep;
+      const bool wide_store = P.mode == TTD_EPI_WGRAD && (P.block_n % 32) == 0 && (P.N % 4) == 0 && (P.ldf % 4) == 0 &&
+                              (reinterpret_cast<uintptr_t>(P.outf) & 15u) == 0;
       const uint32_t drop_thresh = static_cast<uint32_t>(fminf(P.drop_rate, 1.0f) * 4294967040.0f);
       for (int c = 0; c < nchunks; ++c) {
         const int n0 = nbase + c * 16;
         __syncwarp();                      // tcgen05.ld is warp-collective: reconverge before it
         tmem_ld16(taddr_row + c * 16, v);
         const bool live = row_ok && n0 < P.N;
-        if (live && P.mode == TTD_EPI_WGRAD) {
+        if (P.mode == TTD_EPI_WGRAD && wide_store) {
+          // 32 rows x 32 fp32 columns per warp go through a private smem patch (the pipeline stages are idle
+          // by now) so that every global store instruction writes whole 128-byte lines of four rows instead
+          // of 16 bytes of thirty-two rows
+          float v2[16];
+          __syncwarp();
+          tmem_ld16(taddr_row + c * 16 + 16, v2);
+          float* patch = reinterpret_cast<float*>(smem) + (warp - 4) * (32 * 36);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            *reinterpret_cast<float4*>(patch + lane * 36 + 4 * q) =
+                make_float4(v[4 * q] * P.scale, v[4 * q + 1] * P.scale, v[4 * q + 2] * P.scale, v[4 * q + 3] * P.scale);
+            *reinterpret_cast<float4*>(patch + lane * 36 + 16 + 4 * q) =
+                make_float4(v2[4 * q] * P.scale, v2[4 * q + 1] * P.scale, v2[4 * q + 2] * P.scale, v2[4 * q + 3] * P.scale);
+          }
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int rl = i * 4 + (lane >> 3), c4 = (lane & 7) * 4;
+            const int mm = m0 + quad * 32 + rl, nn = n0 + c4;
+            if (mm < P.M && nn < P.N)  // N % 4 == 0 in this mode, so a float4 never straddles the edge
+              *reinterpret_cast<float4*>(P.outf + static_cast<long long>(mm) * P.ldf + nn) =
+                  *reinterpret_cast<const float4*>(patch + rl * 36 + c4);
+          }
+          ++c;  // two 16-column chunks consumed
+        } else if (live && P.mode == TTD_EPI_WGRAD) {
           float* row = P.outf + static_cast<long long>(m) * P.ldf;
           const bool vec = ((reinterpret_cast<uintptr_t>(row + n0) & 15u) == 0) && (n0 + 16 <= P.N);
           if (vec) {
@@ -339,6 +385,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
 
   tc_fence_before();
   __syncthreads();
+  if (cl > 1) {  // nobody leaves while a peer may still signal one of its barriers
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  }
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, static_cast<uint32_t>(g.tmem_cols));
@@ -452,7 +502,15 @@ extern "C" int ttd_gemm_group(const TtdGemmDesc* d, int count, uint64_t seed, co
       set_error("ttd_gemm_group: out must be 16-byte aligned with ldo %% 8 == 0");
       return -1;
     }
-    int rc = make_tmap(&P.tma_a, s.a, s.M, s.K, s.lda, kBlockM);
+    // A shared by a cluster: skinny problems (one M tile) whose CTAs all stream the same activations
+    int cluster = 1;
+    if (count == 1 && !(flags & 2u) && s.M <= kBlockM && s.K >= 512) {
+      const int tn = (s.N + bn - 1) / bn;
+      if (tn >= 8 && tn % 4 == 0) cluster = 4;
+      else if (tn >= 4 && tn % 2 == 0) cluster = 2;
+    }
+    g.cluster = cluster;
+    int rc = make_tmap(&P.tma_a, s.a, s.M, s.K, s.lda, kBlockM / cluster);
     if (rc) return rc;
     rc = make_tmap(&P.tma_b, s.b, s.N, s.K, s.ldb, bn);
     if (rc) return rc;
@@ -515,8 +573,15 @@ extern "C" int ttd_gemm_group(const TtdGemmDesc* d, int count, uint64_t seed, co
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = smem_bytes;
   cfg.stream = static_cast<cudaStream_t>(stream);
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   int nattr = 0;
+  if (g.cluster > 1) {
+    attr[nattr].id = cudaLaunchAttributeClusterDimension;
+    attr[nattr].val.clusterDim.x = static_cast<unsigned>(g.cluster);
+    attr[nattr].val.clusterDim.y = 1;
+    attr[nattr].val.clusterDim.z = 1;
+    ++nattr;
+  }
   if (g.use_pdl) {
     attr[nattr].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[nattr].val.programmaticStreamSerializationAllowed = 1;

@@ -26,6 +26,10 @@ def ops():
     (128, 128, 64, 0), (128, 128, 256, 0), (128, 16, 64, 0), (128, 25, 50, 0), (128, 256, 128, 256),
     (785, 200, 128, 0), (128, 200, 784, 0), (201, 100, 128, 0), (512, 1024, 2048, 0), (128, 512, 8192, 64),
     (100, 10, 25, 0), (64, 8192, 784, 0),
+    (128, 2048, 1024, 64),   # 32 N tiles -> clusters of 4 share the A tile by TMA multicast
+    (100, 512, 512, 128),    # 4 N tiles -> clusters of 2
+    (128, 8192, 8192, 64),   # the wide-MLP forward shape
+    (300, 96, 128, 32), (1025, 512, 128, 0),  # wgrad-like: smem-staged, line-coalesced fp32 stores
 ])
 def test_gemm_matches_fp32_matmul(ops, M, Nn, K, bn):
     N, gemm = ops
