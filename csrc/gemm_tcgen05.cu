@@ -14,6 +14,7 @@
 #include <math.h>
 #include <atomic>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../include/ttd_b200.h"
@@ -67,6 +68,7 @@ struct GemmGroup {
   int tmem_cols;
   int use_pdl;
   int cluster;  // >1: CTAs of a cluster own consecutive N tiles of one M tile and share the A tile by TMA multicast
+  int kspan;    // k-blocks (of 64) per pipeline stage: 2 halves the barrier traffic of long-K weight-streaming GEMMs
 };
 
 __device__ __forceinline__ void store_bf16x8(__nv_bfloat16* dst, const float* v) {
@@ -107,8 +109,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int stages = g.stages;
+  const int kspan = g.kspan;
+  const int a_stage = kAStageBytes * kspan;  // a stage holds kspan k-blocks of each operand, back to back
   uint8_t* sA = smem;
-  uint8_t* sB = smem + stages * kAStageBytes;
+  uint8_t* sB = smem + stages * a_stage;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(sB + stages * g.b_stage_bytes);
   uint64_t* empty_bar = full_bar + stages;
   uint64_t* tmem_full_bar = empty_bar + stages;
@@ -133,7 +137,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
   const int tile_n = cl > 1 ? tile % P.tiles_n : tile / P.tiles_m;
   const int m0 = tile_m * kBlockM;
   const int nbase = tile_n * P.block_n;
-  const int num_kb = (P.K + kBlockK - 1) / kBlockK;
+  const int num_kb = ((P.K + kBlockK - 1) / kBlockK + kspan - 1) / kspan;  // pipeline iterations
 
   const bool pull_fused = (pi == 0 && g.n_b_peers > 0);
   if (warp == 0 && lane == 0) {
@@ -172,28 +176,33 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      const uint32_t tx_bytes = kAStageBytes + P.block_n * kBlockK * 2;
+      const int b_kb_bytes = P.block_n * kBlockK * 2;
+      const uint32_t tx_bytes = static_cast<uint32_t>(kspan * (kAStageBytes + b_kb_bytes));
       int s = 0;
       uint32_t ph = 0;
       int owner = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const CUtensorMap* map_b = &P.tma_b;
-        if (pull_fused) {
-          while (owner + 1 < g.n_b_peers && kb >= g.kb_bound[owner + 1]) ++owner;
-          map_b = &g.tma_b_peer[owner];  // remote HBM over NVLink, same coordinates as the local copy
-        }
+      for (int it = 0; it < num_kb; ++it) {
         mbar_wait(&empty_bar[s], ph ^ 1u);
         mbar_arrive_expect_tx(&full_bar[s], tx_bytes);
-        if (cl > 1) {
-          // this CTA fetches 1/cl of the A tile and the TMA unit delivers it to every CTA of the cluster:
-          // A crosses the L2->SM fabric once per cluster instead of once per CTA
-          const int rows = kBlockM / cl;
-          tma_load_2d_mcast(sA + s * kAStageBytes + cta_rank * rows * (kBlockK * 2), &P.tma_a, &full_bar[s],
-                            kb * kBlockK, m0 + static_cast<int>(cta_rank) * rows, cl_mask);
-        } else {
-          tma_load_2d(sA + s * kAStageBytes, &P.tma_a, &full_bar[s], kb * kBlockK, m0);
+        for (int j = 0; j < kspan; ++j) {
+          const int kb = it * kspan + j;  // beyond K the box is out of bounds and arrives as zeros
+          const CUtensorMap* map_b = &P.tma_b;
+          if (pull_fused) {
+            while (owner + 1 < g.n_b_peers && kb >= g.kb_bound[owner + 1]) ++owner;
+            map_b = &g.tma_b_peer[owner];  // remote HBM over NVLink, same coordinates as the local copy
+          }
+          uint8_t* dst_a = sA + s * a_stage + j * kAStageBytes;
+          if (cl > 1) {
+            // this CTA fetches 1/cl of the A tile and the TMA unit delivers it to every CTA of the cluster:
+            // A crosses the L2->SM fabric once per cluster instead of once per CTA
+            const int rows = kBlockM / cl;
+            tma_load_2d_mcast(dst_a + cta_rank * rows * (kBlockK * 2), &P.tma_a, &full_bar[s], kb * kBlockK,
+                              m0 + static_cast<int>(cta_rank) * rows, cl_mask);
+          } else {
+            tma_load_2d(dst_a, &P.tma_a, &full_bar[s], kb * kBlockK, m0);
+          }
+          tma_load_2d(sB + s * g.b_stage_bytes + j * b_kb_bytes, map_b, &full_bar[s], kb * kBlockK, nbase);
         }
-        tma_load_2d(sB + s * g.b_stage_bytes, map_b, &full_bar[s], kb * kBlockK, nbase);
         if (++s == stages) { s = 0; ph ^= 1u; }
       }
     }
@@ -206,13 +215,16 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&full_bar[s], ph);
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(sA + s * kAStageBytes);
+        const uint32_t a_addr = smem_u32(sA + s * a_stage);
         const uint32_t b_addr = smem_u32(sB + s * g.b_stage_bytes);
+        const uint32_t b_kb_bytes = static_cast<uint32_t>(P.block_n * kBlockK * 2);
+        for (int j = 0; j < kspan; ++j) {
 #pragma unroll
-        for (int k = 0; k < kBlockK / 16; ++k) {
-          const uint64_t da = umma_desc_k_sw128(a_addr + k * 32);
-          const uint64_t db = umma_desc_k_sw128(b_addr + k * 32);
-          umma_bf16_ss(tmem_base, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            const uint64_t da = umma_desc_k_sw128(a_addr + j * kAStageBytes + k * 32);
+            const uint64_t db = umma_desc_k_sw128(b_addr + j * b_kb_bytes + k * 32);
+            umma_bf16_ss(tmem_base, da, db, idesc, (kb | j | k) != 0 ? 1u : 0u);
+          }
         }
         if (cl > 1) umma_commit_mcast(&empty_bar[s], cl_mask);  // tell every producer that feeds this slot
         else umma_commit(&empty_bar[s]);                       // smem slot reusable once these MMAs have drained
@@ -429,8 +441,17 @@ static int make_tmap(CUtensorMap* map, const void* base, int64_t rows, int64_t c
   cuuint64_t gstride[1] = {static_cast<cuuint64_t>(ld) * 2};
   cuuint32_t box[2] = {static_cast<cuuint32_t>(kBlockK), static_cast<cuuint32_t>(box_rows)};
   cuuint32_t estr[2] = {1, 1};
+  static int promo = -1;
+  if (promo < 0) {
+    const char* e = getenv("TTD_GEMM_L2PROMO");  // tuning knob: 0 none, 1 64B, 2 128B, 3 256B (default)
+    promo = e ? atoi(e) : 3;
+  }
+  const CUtensorMapL2promotion l2p = promo == 0   ? CU_TENSOR_MAP_L2_PROMOTION_NONE
+                                     : promo == 1 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+                                     : promo == 2 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B
+                                                  : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, l2p,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed: CUresult %d (rows=%lld cols=%lld ld=%lld box_rows=%d)", (int)r,
@@ -508,6 +529,10 @@ extern "C" int ttd_gemm_group(const TtdGemmDesc* d, int count, uint64_t seed, co
       const int tn = (s.N + bn - 1) / bn;
       if (tn >= 8 && tn % 4 == 0) cluster = 4;
       else if (tn >= 4 && tn % 2 == 0) cluster = 2;
+      if (const char* e = getenv("TTD_GEMM_CLUSTER")) {  // tuning knob: force 1 / 2 / 4
+        const int want = atoi(e);
+        if (want == 1 || (want > 1 && tn % want == 0 && want <= 8)) cluster = want;
+      }
     }
     g.cluster = cluster;
     int rc = make_tmap(&P.tma_a, s.a, s.M, s.K, s.lda, kBlockM / cluster);
@@ -548,9 +573,14 @@ extern "C" int ttd_gemm_group(const TtdGemmDesc* d, int count, uint64_t seed, co
     P.metrics = s.metrics;
     if (bn > max_bn) max_bn = bn;
   }
-  g.b_stage_bytes = max_bn * kBlockK * 2;
+  // long-K problems pack two k-blocks per stage (half the barrier round trips per byte streamed)
+  int max_k = 0;
+  for (int i = 0; i < count; ++i) max_k = d[i].K > max_k ? d[i].K : max_k;
+  g.kspan = max_k >= 2048 ? 2 : 1;
+  if (const char* e = getenv("TTD_GEMM_KSPAN")) g.kspan = atoi(e) >= 2 ? 2 : 1;
+  g.b_stage_bytes = max_bn * kBlockK * 2 * g.kspan;
   if (g.b_stage_bytes < 1024) g.b_stage_bytes = 1024;
-  const int stage_bytes = kAStageBytes + g.b_stage_bytes;
+  const int stage_bytes = kAStageBytes * g.kspan + g.b_stage_bytes;
   int stages = (200 * 1024) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) stages = 2;
