@@ -51,6 +51,7 @@ struct GemmProblem {
   float scale;
   const long long* labels;
   float* metrics;
+  int swap;  // 1: operands were exchanged by the host (rows of the tile = output features, columns = batch)
 };
 
 struct GemmGroup {
@@ -353,6 +354,52 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
             for (int j = 0; j < 16; ++j)
               if (n0 + j < P.N) row[n0 + j] = v[j] * P.scale;
           }
+        } else if (live && P.swap) {
+          // Weight-stationary orientation: this thread owns output feature f = m and the 16 columns are
+          // consecutive batch rows. All pointers keep their logical [batch, feature] meaning.
+          const int f = m;
+          const float bias_f = (P.mode == TTD_EPI_FWD && P.bias) ? P.bias[f] : 0.0f;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int b = n0 + j;
+            float r = 0.0f;
+            if (b < P.N) {
+              bool kept = true;
+              if (P.drop_rate > 0.0f) {
+                const Philox4 rnd = dropout_block(static_cast<uint32_t>(b), static_cast<uint32_t>(f >> 2), step,
+                                                  P.layer_id, g.seed_lo, g.seed_hi);
+                kept = philox_pick(rnd, f & 3) >= drop_thresh;
+              }
+              if (P.mode == TTD_EPI_FWD) {
+                const float a = act_apply(v[j] + bias_f, P.act);
+                if (P.outf) P.outf[static_cast<long long>(b) * P.ldf + f] = a;
+                r = kept ? a * inv_keep : 0.0f;
+              } else {  // DGRAD
+                const float a_sv = P.aux ? __bfloat162float(P.aux[static_cast<long long>(b) * P.ldaux + f]) : 1.0f;
+                r = kept ? v[j] * inv_keep * act_grad_from_out(a_sv * keep, P.act) : 0.0f;
+              }
+            }
+            v[j] = r;
+          }
+          if (P.out != nullptr) {  // [batch, feature]: lanes are consecutive features -> coalesced
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (n0 + j < P.N) P.out[static_cast<long long>(n0 + j) * P.ldo + f] = __float2bfloat16(v[j]);
+          }
+          if (P.outT != nullptr) {  // [feature, batch]: 16 consecutive batch entries of this thread's row
+            __nv_bfloat16* row = P.outT + static_cast<long long>(f) * P.ldt;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const int nb = n0 + 8 * h;
+              if (nb + 8 <= P.ldt) {
+                store_bf16x8(row + nb, v + 8 * h);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  if (nb + j < P.N) row[nb + j] = __float2bfloat16(v[8 * h + j]);
+              }
+            }
+          }
         } else if (live) {
           float a_saved[16];
           if (P.mode == TTD_EPI_DGRAD && P.aux != nullptr) {
@@ -493,11 +540,23 @@ extern "C" int ttd_gemm_group(const TtdGemmDesc* d, int count, uint64_t seed, co
   g.use_pdl = (flags & 1u) ? 1 : 0;
   int total_tiles = 0, max_bn = 16;
   for (int i = 0; i < count; ++i) {
-    const TtdGemmDesc& s = d[i];
+    TtdGemmDesc s = d[i];  // local copy: the operands may be exchanged below
     GemmProblem& P = g.p[i];
     if (s.M < 1 || s.N < 1 || s.K < 1) {
       set_error("ttd_gemm_group: problem %d has empty shape %dx%dx%d", i, s.M, s.N, s.K);
       return -1;
+    }
+    // Skinny-batch forward / dgrad over a wide layer: exchange the operands so that every CTA streams a
+    // 128-row slab of the WEIGHTS (the expensive operand) and only a 64-row slice of the activations shares
+    // its pipeline stages: twice the weight bytes in flight per SM, which is what a latency-bound stream needs.
+    const bool swap = (s.mode == TTD_EPI_FWD || s.mode == TTD_EPI_DGRAD) && s.M <= 256 && s.N >= 1024 &&
+                      !(flags & 4u) && !(i == 0 && s.n_b_peers > 0);
+    if (swap) {  // out / outT / outf / aux / bias keep their logical [batch, feature] meaning (see the epilogue)
+      const TtdGemmDesc o = s;
+      s.a = o.b; s.lda = o.ldb;
+      s.b = o.a; s.ldb = o.lda;
+      s.M = o.N; s.N = o.M;
+      s.block_n = o.M >= 64 ? 64 : ((o.M + 15) / 16) * 16;
     }
     int bn = s.block_n > 0 ? s.block_n : choose_block_n(s.M, s.N);
     if (bn % 16 != 0 || bn < 16 || bn > 256) {
@@ -571,6 +630,7 @@ extern "C" int ttd_gemm_group(const TtdGemmDesc* d, int count, uint64_t seed, co
     P.scale = s.scale;
     P.labels = reinterpret_cast<const long long*>(s.labels);
     P.metrics = s.metrics;
+    P.swap = swap ? 1 : 0;
     if (bn > max_bn) max_bn = bn;
   }
   // long-K problems pack two k-blocks per stage (half the barrier round trips per byte streamed)

@@ -74,11 +74,13 @@ def make_desc(a: torch.Tensor, b: torch.Tensor, M: int, Nn: int, K: int, mode: i
 
 
 def gemm_group(descs: Sequence[N.GemmDesc], *, seed: int = 0, step_ptr: Optional[int] = None, pdl: bool = False,
-               stream: Optional[int] = None) -> None:
-    """Launch 1..4 problems as one kernel on the current stream."""
+               stream: Optional[int] = None, no_cluster: bool = False, no_swap: bool = False) -> None:
+    """Launch 1..4 problems as one kernel on the current stream. ``no_cluster`` / ``no_swap`` switch off the
+    A-multicast clusters and the weight-stationary operand exchange (tests compare both code paths)."""
     lib = N.load()
     arr = (N.GemmDesc * len(descs))(*descs)
-    rc = lib.ttd_gemm_group(arr, len(descs), C.c_uint64(seed & (2**64 - 1)), step_ptr, 1 if pdl else 0,
+    flags = (1 if pdl else 0) | (2 if no_cluster else 0) | (4 if no_swap else 0)
+    rc = lib.ttd_gemm_group(arr, len(descs), C.c_uint64(seed & (2**64 - 1)), step_ptr, flags,
                             stream if stream is not None else N.cur_stream())
     N.check(rc, "ttd_gemm_group")
 

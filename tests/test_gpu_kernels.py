@@ -278,3 +278,36 @@ def test_pull_fused_b_operand_reads_each_k_range_from_its_owner(ops):
     ref = a[:, :K].float() @ b[:, :K].float().t()
     assert torch.isfinite(out).all()
     assert torch.allclose(out, ref, rtol=1e-4, atol=1e-3 * K ** 0.5)
+
+
+@pytest.mark.parametrize("mode", ["fwd", "dgrad"])
+def test_weight_stationary_orientation_matches_plain_orientation(ops, mode):
+    """Wide layers run with exchanged operands (tile rows = features); results and dropout masks must not care."""
+    N, gemm = ops
+    M, Nn, K, rate = 128, 2048, 512, 0.1
+    a, b = _mk(M, K, scale=0.05, seed=31), _mk(Nn, K, seed=32)
+    bias = torch.randn(Nn, device="cuda")
+    aux = _mk(M, Nn, seed=33)
+    step = torch.tensor([3], device="cuda", dtype=torch.int64)
+    res = []
+    for no_swap in (True, False):
+        out = torch.zeros(M, Nn, device="cuda", dtype=torch.bfloat16)
+        outT = torch.zeros(Nn + 1, M, device="cuda", dtype=torch.bfloat16)
+        outf = torch.zeros(M, Nn, device="cuda") if mode == "fwd" else None
+        if mode == "fwd":
+            d = gemm.make_desc(a, b, M, Nn, K, N.EPI_FWD, act=N.ACT_ELU, drop_rate=rate, layer_id=2, bias=bias, out=out,
+                               outT=outT, outf=outf)
+        else:
+            d = gemm.make_desc(a, b, M, Nn, K, N.EPI_DGRAD, act=N.ACT_ELU, drop_rate=rate, layer_id=2, aux=aux, out=out,
+                               outT=outT)
+        gemm.gemm_group([d], seed=99, step_ptr=step.data_ptr(), no_swap=no_swap, no_cluster=True)
+        torch.cuda.synchronize()
+        res.append((out.clone(), outT.clone(), None if outf is None else outf.clone()))
+    (o0, t0, f0), (o1, t1, f1) = res
+    assert torch.equal(o0 != 0, o1 != 0)                       # identical dropout pattern
+    assert torch.allclose(o0.float(), o1.float(), rtol=1e-2, atol=1e-3)
+    assert torch.equal(t1[:Nn].t().contiguous(), o1)           # both copies agree in the exchanged orientation too
+    if mode == "fwd":
+        ref = torch.nn.functional.elu(a.float() @ b.float().t() + bias)
+        assert torch.allclose(f1, ref, rtol=1e-3, atol=1e-3) and torch.allclose(f0, f1, rtol=1e-5, atol=1e-5)
+        assert abs((o1 == 0).float().mean().item() - rate) < 0.02

@@ -21,7 +21,7 @@ def main():
     which = sys.argv[1] if len(sys.argv) > 1 else "fwd"
     iters = int(sys.argv[2]) if len(sys.argv) > 2 else 20
     bn = int(sys.argv[3]) if len(sys.argv) > 3 else 0
-    B, H = 128, 8192
+    B, H = int(os.environ.get("GP_BATCH", "128")), 8192
     if which == "fwd":      # Z[B,H] = A[B,H] . Wt[H,H]^T  (+bias, relu)
         a, b = mk(B, H, 1), mk(H, H, 2)
         out = torch.zeros(B, H, device="cuda", dtype=torch.bfloat16)
