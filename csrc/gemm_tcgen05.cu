@@ -643,7 +643,11 @@ extern "C" int ttd_gemm_group(const TtdGemmDesc* d, int count, uint64_t seed, co
   const int stage_bytes = kAStageBytes * g.kspan + g.b_stage_bytes;
   int stages = (200 * 1024) / stage_bytes;
   if (stages > 8) stages = 8;
-  if (stages < 2) stages = 2;
+  if (const char* e = getenv("TTD_GEMM_STAGES")) {  // tuning knob
+    const int want = atoi(e);
+    if (want >= 1 && want < stages) stages = want;
+  }
+  if (stages < 1) stages = 1;
   g.stages = stages;
   int tmem_cols = 32;
   while (tmem_cols < max_bn) tmem_cols <<= 1;

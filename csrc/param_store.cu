@@ -44,6 +44,7 @@ struct PeerInfo {
   long long copy_delta[kMaxPeers];   // byte offset from a local bf16-copy pointer to replica r's copy
   uint32_t* flags[kMaxPeers];        // signal pad of every replica: [grid][kMaxPeers] u32
   const float* grads_mc;             // multicast mapping of the gradient buffer (NVLS) or NULL
+  long long mc_delta;                // byte distance from a local arena address to its multicast alias (0: none)
   int n_grads;                       // replicas contributing gradients
   int n_copies;                      // replicas receiving the bf16 copies
   int rank;
@@ -122,6 +123,45 @@ __device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const float* mc_addr)
   return r;
 }
 
+// one store, delivered by the NVSwitch to the same offset of every replica's arena
+__device__ __forceinline__ void multimem_st_b128(void* mc_addr, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr),
+               "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+               : "memory");
+}
+__device__ __forceinline__ void multimem_st_b64(void* mc_addr, uint2 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(mc_addr), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y))
+               : "memory");
+}
+__device__ __forceinline__ float4 ld_cv_f32x4(const float* p) {
+  float4 r;
+  asm volatile("ld.global.cv.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  const __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&t);
+}
+// Store `bytes` (8 or 16) to the local copy and to every other replica's copy: through the multicast alias
+// when the fabric offers one, else one NVLink store per replica.
+template <typename VecT>
+__device__ __forceinline__ void broadcast_store(const PeerInfo& pi, void* local_ptr, VecT v, bool local_only) {
+  if (local_only || pi.n_copies <= 1) {
+    *reinterpret_cast<VecT*>(local_ptr) = v;
+    return;
+  }
+  if (pi.mc_delta != 0) {
+    void* mc = reinterpret_cast<char*>(local_ptr) + pi.mc_delta;
+    if constexpr (sizeof(VecT) == 16) multimem_st_b128(mc, *reinterpret_cast<uint4*>(&v));
+    else multimem_st_b64(mc, *reinterpret_cast<uint2*>(&v));
+    return;
+  }
+#pragma unroll
+  for (int q = 0; q < kMaxPeers; ++q)
+    if (q < pi.n_copies) *reinterpret_cast<VecT*>(reinterpret_cast<char*>(local_ptr) + pi.copy_delta[q]) = v;
+}
+
 __device__ __forceinline__ float trunc_normal(uint64_t seed, uint64_t idx) {
   // Philox + Box-Muller, resampled until |z| <= 2 (TF truncated_normal), deterministic in (seed, idx)
   for (uint32_t attempt = 0; attempt < 16; ++attempt) {
@@ -196,6 +236,98 @@ __global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarT
     if (t_hi <= lo || t_lo >= hi) continue;
 
     __syncthreads();  // previous tile's transposed reads are done
+    if (MODE == kUpdate && (C & 3) == 0) {
+      // ---- vector tile (row pitch a multiple of 4): 128-bit traffic end to end ----------------------------
+      // thread -> row tid/8, four columns at 4*(tid%8). Gradients: ONE multimem.ld_reduce (the NVSwitch adds the
+      // replicas' values in flight) or one 16-byte load per replica; copies: multimem.st / 8- and 16-byte stores.
+      const int rl = threadIdx.x >> 3, cg = threadIdx.x & 7;
+      const int r = r0 + rl, c = c0 + 4 * cg;
+      const long long idx = V.offset + static_cast<long long>(r) * C + c;
+      const bool ok = r < R && c < C && idx >= lo && idx + 3 < hi;
+      float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f), w4 = g4, s4 = g4;
+      const bool use_ema = ema != nullptr && h.ema_decay > 0.0f;
+      if (ok) {
+        if (pi.grads_mc != nullptr) {
+          g4 = multimem_ld_reduce_f32x4(pi.grads_mc + idx);
+        } else {
+#pragma unroll
+          for (int q = 0; q < kMaxPeers; ++q)
+            if (q < pi.n_grads) {
+              const float4 t4 = ld_cv_f32x4(pi.grads[q] + idx);
+              g4.x += t4.x; g4.y += t4.y; g4.z += t4.z; g4.w += t4.w;
+            }
+        }
+        w4 = *reinterpret_cast<const float4*>(w + idx);
+        if (use_ema) s4 = *reinterpret_cast<const float4*>(ema + idx);
+      }
+      if (trace) {
+        if (tr_ntiles == 0) {
+          if (g4.x + g4.y == 123.456f) st->reserved[5] = 1;  // the loads must have landed before the clock is read
+          tr_loads = static_cast<uint32_t>(globaltimer_ns() - k_t0);
+        }
+        ++tr_ntiles;
+      }
+      float val[4] = {0.f, 0.f, 0.f, 0.f};
+      if (ok) {
+        const float gv[4] = {g4.x, g4.y, g4.z, g4.w}, wv4[4] = {w4.x, w4.y, w4.z, w4.w}, sv[4] = {s4.x, s4.y, s4.z, s4.w};
+        float nv[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float g = gv[i] * h.grad_scale;
+          if (V.regularize && r < V.rows) {
+            if (h.reg_kind == 2) g += h.reg_scale * wv4[i];
+            else if (h.reg_kind == 1) g += h.reg_scale * (wv4[i] > 0.0f ? 1.0f : (wv4[i] < 0.0f ? -1.0f : 0.0f));
+          }
+          val[i] = wv4[i] - lr * g;
+          nv[i] = sv[i] - (1.0f - ema_d) * (sv[i] - val[i]);
+        }
+        *reinterpret_cast<float4*>(w + idx) = make_float4(val[0], val[1], val[2], val[3]);
+        if (use_ema) *reinterpret_cast<float4*>(ema + idx) = make_float4(nv[0], nv[1], nv[2], nv[3]);
+        if (V.bias_c != nullptr && r == V.rows)
+          broadcast_store<float4>(pi, V.bias_c + c, make_float4(val[0], val[1], val[2], val[3]), false);
+        if (V.w_rm != nullptr && r < V.rows) {
+          const uint2 packed = make_uint2(pack_bf16x2(val[0], val[1]), pack_bf16x2(val[2], val[3]));
+          broadcast_store<uint2>(pi, static_cast<__nv_bfloat16*>(V.w_rm) + static_cast<long long>(r) * V.ld_rm + c, packed,
+                                 false);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        tile[rl][4 * cg + i] = val[i];
+        tile_ok[rl][4 * cg + i] = ok ? 1 : 0;
+      }
+      if (V.w_t != nullptr) {
+        __syncthreads();
+        if (threadIdx.x < 128) {  // thread -> column tid/4, eight rows at 8*(tid%4): one 16-byte store of 8 bf16
+          const int cl = threadIdx.x >> 2, rg = threadIdx.x & 3;
+          const int cc = c0 + cl, rr0 = r0 + 8 * rg;
+          bool all_ok = cc < C && rr0 + 7 < V.rows;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) all_ok = all_ok && tile_ok[8 * rg + i][cl];
+          __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(V.w_t) + static_cast<long long>(cc) * V.ld_t + rr0;
+          const bool local_only = (V.reserved & 1) != 0;  // operand fetched from its owner by the pull-fused GEMM
+          if (all_ok) {
+            uint4 pk;
+            pk.x = pack_bf16x2(tile[8 * rg + 0][cl], tile[8 * rg + 1][cl]);
+            pk.y = pack_bf16x2(tile[8 * rg + 2][cl], tile[8 * rg + 3][cl]);
+            pk.z = pack_bf16x2(tile[8 * rg + 4][cl], tile[8 * rg + 5][cl]);
+            pk.w = pack_bf16x2(tile[8 * rg + 6][cl], tile[8 * rg + 7][cl]);
+            broadcast_store<uint4>(pi, dst, pk, local_only);
+          } else if (cc < C) {
+            for (int i = 0; i < 8; ++i) {
+              if (tile_ok[8 * rg + i][cl] && rr0 + i < V.rows) {
+                const __nv_bfloat16 bv = __float2bfloat16(tile[8 * rg + i][cl]);
+                for (int q = 0; q < pi.n_copies; ++q) {
+                  if (local_only && pi.copy_delta[q] != 0) continue;
+                  *reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(dst + i) + pi.copy_delta[q]) = bv;
+                }
+              }
+            }
+          }
+        }
+      }
+      continue;
+    }
     // phase 1: addresses + every load of this thread's four elements issued back to back, so the NVLink
     // round trips to the peers' gradient buffers overlap instead of queueing behind one another
     long long idxs[kTile / 8];
@@ -449,6 +581,7 @@ extern "C" int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars, in
     pi.flags[i] = peers->flags[i];
   }
   pi.grads_mc = peers->grads_mc;
+  pi.mc_delta = peers->mc_delta;
   pi.n_grads = peers->n_grads;
   pi.n_copies = peers->n_copies;
   pi.rank = peers->rank;

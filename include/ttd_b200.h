@@ -133,6 +133,7 @@ typedef struct TtdPeers {
   int64_t copy_delta[TTD_MAX_PEERS];   /* byte distance from a local bf16-copy address to replica r's */
   uint32_t* flags[TTD_MAX_PEERS];      /* replica r's signal pad: u32[grid][TTD_MAX_PEERS], zero-initialised */
   const float* grads_mc;               /* multicast (NVLS) mapping of the gradient buffers, or NULL */
+  int64_t mc_delta;                    /* byte distance from a local arena address to its multicast alias; 0 = none */
   int32_t n_grads, n_copies, rank;
   int32_t barrier;                     /* 1: bracket the update with cross-replica barriers */
   int32_t grid;                        /* barrier mode: CTA count, identical on all replicas, <= 148 */

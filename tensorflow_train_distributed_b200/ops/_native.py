@@ -98,6 +98,7 @@ class Peers(C.Structure):
         ("copy_delta", C.c_int64 * MAX_PEERS),
         ("flags", C.c_void_p * MAX_PEERS),
         ("grads_mc", C.c_void_p),
+        ("mc_delta", C.c_int64),
         ("n_grads", C.c_int32), ("n_copies", C.c_int32), ("rank", C.c_int32),
         ("barrier", C.c_int32),
         ("grid", C.c_int32),

@@ -66,6 +66,8 @@ class GpuParamStore:
         # K3: the first layer's transposed weights are not broadcast after an update; every replica's first
         # GEMM fetches each k-block from its owner by TMA over NVLink instead
         self.pull_fused_first = bool(pull_fused_first and comm is not None)
+        import os as _os
+        self.use_multicast = _os.environ.get("TTD_NVLS", "1") != "0"
         self.lib = N.load()
         self.world = comm.world_size if comm is not None else 1
         self.rank = comm.rank if comm is not None else 0
@@ -153,7 +155,10 @@ class GpuParamStore:
             p.grads[r] = base[r]  # the arena starts with the gradient buffer
             p.copy_delta[r] = base[r] - base[self.rank]
             p.flags[r] = base[r] + self._flags_off
-        p.grads_mc = None
+        mc = self._arena.multicast_ptr if self.use_multicast else 0
+        if mc:  # NVLS: the switch sums the replicas' gradients and replicates the refreshed copies
+            p.grads_mc = mc + self._off["grads"]
+            p.mc_delta = mc - base[self.rank]
         p.n_grads = p.n_copies = self.world
         p.rank = self.rank
         p.barrier = 1
