@@ -178,7 +178,7 @@ __device__ __forceinline__ float trunc_normal(uint64_t seed, uint64_t idx) {
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(256) param_kernel(const __grid_constant__ VarTable vt, float* __restrict__ w,
+__global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ VarTable vt, float* __restrict__ w,
                                                     float* __restrict__ ema, const __grid_constant__ PeerInfo pi,
                                                     long long lo, long long hi, TtdHyper h, TtdStepState* st,
                                                     int bump_global_step, unsigned long long seed) {
@@ -589,8 +589,8 @@ extern "C" int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars, in
   int grid = grid_for(vt.tile_begin[vt.n] > 0 ? vt.tile_begin[vt.n] : 1);
   if (pi.barrier) {
     // blocks of different replicas wait on one another: all of them must be resident at once
-    if (peers->grid <= 0 || peers->grid > 148) {
-      set_error("ttd_apply_update: barrier mode needs an explicit grid in [1,148], got %d", peers->grid);
+    if (peers->grid <= 0 || peers->grid > 148 * 4) {
+      set_error("ttd_apply_update: barrier mode needs an explicit grid in [1,592], got %d", peers->grid);
       return -1;
     }
     grid = peers->grid;

@@ -136,7 +136,7 @@ typedef struct TtdPeers {
   int64_t mc_delta;                    /* byte distance from a local arena address to its multicast alias; 0 = none */
   int32_t n_grads, n_copies, rank;
   int32_t barrier;                     /* 1: bracket the update with cross-replica barriers */
-  int32_t grid;                        /* barrier mode: CTA count, identical on all replicas, <= 148 */
+  int32_t grid;                        /* barrier mode: CTA count, identical on all replicas, <= 592 (all co-resident) */
   int32_t reserved;
 } TtdPeers;
 

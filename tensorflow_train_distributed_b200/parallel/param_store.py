@@ -28,7 +28,7 @@ import torch
 from ..ops import _native as N
 from .sharding import EMA_SUFFIX, GLOBAL_STEP, FlatPlan, ParamLayout, flat
 
-FLAG_SLOTS = 148  # one signal row per CTA of a barrier-mode launch
+FLAG_SLOTS = 148 * 4  # one signal row per CTA of a barrier-mode launch (<= 4 co-resident CTAs per SM)
 
 
 def _pad8(n: int) -> int:

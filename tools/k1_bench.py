@@ -80,7 +80,7 @@ def main():
     st.hi = hi
     payload = st.layout.total * 4
     if rank == 0:
-        print("K1BENCH " + json.dumps({"world": world, "model": model, "grid": grid, "params": st.layout.num_parameters,
+        print("K1BENCH " + json.dumps({"world": world, "model": model, "grid": grid, "nvls": bool(st._peers.mc_delta), "params": st.layout.num_parameters,
                                        "us": res, "bytes_grad": payload}), flush=True)
     tr.close()
     dist.barrier(device_ids=[comm.device.index])
