@@ -30,7 +30,8 @@ extern std::atomic<uint64_t> g_launch_count;
 
 constexpr int kMaxVars = 16;
 constexpr int kMaxPeers = 8;
-constexpr int kTile = 32;
+constexpr int kTile = 32;    // tile columns
+constexpr int kTileR = 64;   // tile rows: two 128-bit groups per thread in flight on the vector path
 
 struct VarTable {
   TtdVarDesc v[kMaxVars];
@@ -182,8 +183,8 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
                                                     float* __restrict__ ema, const __grid_constant__ PeerInfo pi,
                                                     long long lo, long long hi, TtdHyper h, TtdStepState* st,
                                                     int bump_global_step, unsigned long long seed) {
-  __shared__ float tile[kTile][kTile + 1];
-  __shared__ unsigned char tile_ok[kTile][kTile + 1];
+  __shared__ float tile[kTileR][kTile + 1];
+  __shared__ unsigned char tile_ok[kTileR][kTile + 1];
   __shared__ float s_lr, s_ema_d;
   __shared__ unsigned long long s_lstep;
 
@@ -229,77 +230,103 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
     const int R = V.rows + 1, C = V.cols;
     const int tiles_c = (C + kTile - 1) / kTile;
     const int lt = t - vt.tile_begin[vi];
-    const int r0 = (lt / tiles_c + vt.tile_row0[vi]) * kTile, c0 = (lt % tiles_c) * kTile;
+    const int r0 = (lt / tiles_c + vt.tile_row0[vi]) * kTileR, c0 = (lt % tiles_c) * kTile;
     // quick reject: tile entirely outside [lo, hi)
     const long long t_lo = V.offset + static_cast<long long>(r0) * C;
-    const long long t_hi = V.offset + static_cast<long long>(min(r0 + kTile, R)) * C;
+    const long long t_hi = V.offset + static_cast<long long>(min(r0 + kTileR, R)) * C;
     if (t_hi <= lo || t_lo >= hi) continue;
 
     __syncthreads();  // previous tile's transposed reads are done
     if (MODE == kUpdate && (C & 3) == 0) {
       // ---- vector tile (row pitch a multiple of 4): 128-bit traffic end to end ----------------------------
-      // thread -> row tid/8, four columns at 4*(tid%8). Gradients: ONE multimem.ld_reduce (the NVSwitch adds the
-      // replicas' values in flight) or one 16-byte load per replica; copies: multimem.st / 8- and 16-byte stores.
-      const int rl = threadIdx.x >> 3, cg = threadIdx.x & 7;
-      const int r = r0 + rl, c = c0 + 4 * cg;
-      const long long idx = V.offset + static_cast<long long>(r) * C + c;
-      const bool ok = r < R && c < C && idx >= lo && idx + 3 < hi;
-      float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f), w4 = g4, s4 = g4;
+      // thread -> rows tid/8 and tid/8+32, four columns at 4*(tid%8); both rows' loads are issued before any
+      // arithmetic. Gradients: ONE multimem.ld_reduce per group (the NVSwitch adds the replicas' values in
+      // flight) or one 16-byte load per replica; copies: multimem.st / 16-byte stores.
+      const int cg = threadIdx.x & 7;
+      const int c = c0 + 4 * cg;
       const bool use_ema = ema != nullptr && h.ema_decay > 0.0f;
-      if (ok) {
-        if (pi.grads_mc != nullptr) {
-          g4 = multimem_ld_reduce_f32x4(pi.grads_mc + idx);
-        } else {
+      float4 g4[2], w4[2], s4[2];
+      long long idx2[2];
+      bool ok2[2];
 #pragma unroll
-          for (int q = 0; q < kMaxPeers; ++q)
-            if (q < pi.n_grads) {
-              const float4 t4 = ld_cv_f32x4(pi.grads[q] + idx);
-              g4.x += t4.x; g4.y += t4.y; g4.z += t4.z; g4.w += t4.w;
-            }
+      for (int u = 0; u < 2; ++u) {
+        const int r = r0 + (threadIdx.x >> 3) + 32 * u;
+        const long long idx = V.offset + static_cast<long long>(r) * C + c;
+        const bool ok = r < R && c < C && idx >= lo && idx + 3 < hi;
+        idx2[u] = idx;
+        ok2[u] = ok;
+        g4[u] = w4[u] = s4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok) {
+          if (pi.grads_mc != nullptr) {
+            g4[u] = multimem_ld_reduce_f32x4(pi.grads_mc + idx);
+          } else {
+#pragma unroll
+            for (int q = 0; q < kMaxPeers; ++q)
+              if (q < pi.n_grads) {
+                const float4 t4 = ld_cv_f32x4(pi.grads[q] + idx);
+                g4[u].x += t4.x; g4[u].y += t4.y; g4[u].z += t4.z; g4[u].w += t4.w;
+              }
+          }
+          w4[u] = *reinterpret_cast<const float4*>(w + idx);
+          if (use_ema) s4[u] = *reinterpret_cast<const float4*>(ema + idx);
         }
-        w4 = *reinterpret_cast<const float4*>(w + idx);
-        if (use_ema) s4 = *reinterpret_cast<const float4*>(ema + idx);
       }
       if (trace) {
         if (tr_ntiles == 0) {
-          if (g4.x + g4.y == 123.456f) st->reserved[5] = 1;  // the loads must have landed before the clock is read
+          if (g4[0].x + g4[1].y == 123.456f) st->reserved[5] = 1;  // the loads must have landed before the clock is read
           tr_loads = static_cast<uint32_t>(globaltimer_ns() - k_t0);
         }
         ++tr_ntiles;
       }
-      float val[4] = {0.f, 0.f, 0.f, 0.f};
-      if (ok) {
-        const float gv[4] = {g4.x, g4.y, g4.z, g4.w}, wv4[4] = {w4.x, w4.y, w4.z, w4.w}, sv[4] = {s4.x, s4.y, s4.z, s4.w};
-        float nv[4];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int rl = (threadIdx.x >> 3) + 32 * u, r = r0 + rl;
+        const long long idx = idx2[u];
+        const bool ok = ok2[u];
+        float val[4] = {0.f, 0.f, 0.f, 0.f};
+        if (ok) {
+          const float gv[4] = {g4[u].x, g4[u].y, g4[u].z, g4[u].w}, wv4[4] = {w4[u].x, w4[u].y, w4[u].z, w4[u].w},
+                      sv[4] = {s4[u].x, s4[u].y, s4[u].z, s4[u].w};
+          float nv[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            float g = gv[i] * h.grad_scale;
+            if (V.regularize && r < V.rows) {
+              if (h.reg_kind == 2) g += h.reg_scale * wv4[i];
+              else if (h.reg_kind == 1) g += h.reg_scale * (wv4[i] > 0.0f ? 1.0f : (wv4[i] < 0.0f ? -1.0f : 0.0f));
+            }
+            val[i] = wv4[i] - lr * g;
+            nv[i] = sv[i] - (1.0f - ema_d) * (sv[i] - val[i]);
+          }
+          *reinterpret_cast<float4*>(w + idx) = make_float4(val[0], val[1], val[2], val[3]);
+          if (use_ema) *reinterpret_cast<float4*>(ema + idx) = make_float4(nv[0], nv[1], nv[2], nv[3]);
+          if (V.bias_c != nullptr && r == V.rows)
+            broadcast_store<float4>(pi, V.bias_c + c, make_float4(val[0], val[1], val[2], val[3]), false);
+        }
+        // TF-layout bf16 copy: neighbouring threads pair up so that the even one issues a 16-byte store
+        {
+          const uint32_t p0 = pack_bf16x2(val[0], val[1]), p1 = pack_bf16x2(val[2], val[3]);
+          const uint32_t q0 = __shfl_down_sync(0xffffffffu, p0, 1), q1 = __shfl_down_sync(0xffffffffu, p1, 1);
+          const bool nb_ok = __shfl_down_sync(0xffffffffu, ok ? 1 : 0, 1) != 0;
+          const bool prev_ok = __shfl_up_sync(0xffffffffu, ok ? 1 : 0, 1) != 0;  // (all shuffles before any branch)
+          const bool rows_ok = V.w_rm != nullptr && r < V.rows;
+          __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(V.w_rm) + static_cast<long long>(r) * V.ld_rm + c;
+          if (rows_ok && (cg & 1) == 0 && ok && nb_ok) {
+            broadcast_store<uint4>(pi, dst, make_uint4(p0, p1, q0, q1), false);
+          } else if (rows_ok && ok && ((cg & 1) == 0 || !prev_ok)) {
+            broadcast_store<uint2>(pi, dst, make_uint2(p0, p1), false);
+          }
+        }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          float g = gv[i] * h.grad_scale;
-          if (V.regularize && r < V.rows) {
-            if (h.reg_kind == 2) g += h.reg_scale * wv4[i];
-            else if (h.reg_kind == 1) g += h.reg_scale * (wv4[i] > 0.0f ? 1.0f : (wv4[i] < 0.0f ? -1.0f : 0.0f));
-          }
-          val[i] = wv4[i] - lr * g;
-          nv[i] = sv[i] - (1.0f - ema_d) * (sv[i] - val[i]);
+          tile[rl][4 * cg + i] = val[i];
+          tile_ok[rl][4 * cg + i] = ok ? 1 : 0;
         }
-        *reinterpret_cast<float4*>(w + idx) = make_float4(val[0], val[1], val[2], val[3]);
-        if (use_ema) *reinterpret_cast<float4*>(ema + idx) = make_float4(nv[0], nv[1], nv[2], nv[3]);
-        if (V.bias_c != nullptr && r == V.rows)
-          broadcast_store<float4>(pi, V.bias_c + c, make_float4(val[0], val[1], val[2], val[3]), false);
-        if (V.w_rm != nullptr && r < V.rows) {
-          const uint2 packed = make_uint2(pack_bf16x2(val[0], val[1]), pack_bf16x2(val[2], val[3]));
-          broadcast_store<uint2>(pi, static_cast<__nv_bfloat16*>(V.w_rm) + static_cast<long long>(r) * V.ld_rm + c, packed,
-                                 false);
-        }
-      }
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        tile[rl][4 * cg + i] = val[i];
-        tile_ok[rl][4 * cg + i] = ok ? 1 : 0;
       }
       if (V.w_t != nullptr) {
         __syncthreads();
-        if (threadIdx.x < 128) {  // thread -> column tid/4, eight rows at 8*(tid%4): one 16-byte store of 8 bf16
-          const int cl = threadIdx.x >> 2, rg = threadIdx.x & 3;
+        {  // thread -> column tid/8, eight rows at 8*(tid%8): one 16-byte store of 8 bf16
+          const int cl = threadIdx.x >> 3, rg = threadIdx.x & 7;
           const int cc = c0 + cl, rr0 = r0 + 8 * rg;
           bool all_ok = cc < C && rr0 + 7 < V.rows;
 #pragma unroll
@@ -330,11 +357,11 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
     }
     // phase 1: addresses + every load of this thread's four elements issued back to back, so the NVLink
     // round trips to the peers' gradient buffers overlap instead of queueing behind one another
-    long long idxs[kTile / 8];
-    bool oks[kTile / 8];
-    float gsum[kTile / 8], wold[kTile / 8], sold[kTile / 8];
+    long long idxs[kTileR / 8];
+    bool oks[kTileR / 8];
+    float gsum[kTileR / 8], wold[kTileR / 8], sold[kTileR / 8];
 #pragma unroll
-    for (int rr = 0; rr < kTile / 8; ++rr) {
+    for (int rr = 0; rr < kTileR / 8; ++rr) {
       const int r = r0 + warp + 8 * rr, c = c0 + lane;
       const long long idx = V.offset + static_cast<long long>(r) * C + c;
       const bool ok = r < R && c < C && idx >= lo && idx < hi;
@@ -363,7 +390,7 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
       if (tr_ntiles == 0) {
         float sink = 0.0f;
 #pragma unroll
-        for (int rr = 0; rr < kTile / 8; ++rr) sink += gsum[rr];
+        for (int rr = 0; rr < kTileR / 8; ++rr) sink += gsum[rr];
         if (sink == 123.456f) st->reserved[5] = 1;  // forces the loads to have landed before the clock is read
         tr_loads = static_cast<uint32_t>(globaltimer_ns() - k_t0);
       }
@@ -371,7 +398,7 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
     }
     // phase 2: arithmetic + stores
 #pragma unroll
-    for (int rr = 0; rr < kTile / 8; ++rr) {
+    for (int rr = 0; rr < kTileR / 8; ++rr) {
       const int rl = warp + 8 * rr;
       const int r = r0 + rl, c = c0 + lane;
       const bool ok = oks[rr];
@@ -432,17 +459,20 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
     if (V.w_t != nullptr) {
       __syncthreads();
 #pragma unroll
-      for (int cc = 0; cc < kTile / 8; ++cc) {
-        const int cl = warp + 8 * cc;
-        const int c = c0 + cl, r = r0 + lane;
-        if (tile_ok[lane][cl] && r < V.rows && c < C) {
-          const __nv_bfloat16 b = __float2bfloat16(tile[lane][cl]);
-          for (int q = 0; q < pi.n_copies; ++q) {
-            // flag bit0: consumers fetch this operand from its owner by TMA (pull-fused GEMM), so the
-            // transposed copy is NOT broadcast; only the owner's own buffer is refreshed
-            if ((V.reserved & 1) && pi.copy_delta[q] != 0) continue;
-            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(V.w_t) + pi.copy_delta[q]);
-            dst[static_cast<long long>(c) * V.ld_t + r] = b;
+      for (int half = 0; half < kTileR / 32; ++half) {
+#pragma unroll
+        for (int cc = 0; cc < kTile / 8; ++cc) {
+          const int cl = warp + 8 * cc, rl = lane + 32 * half;
+          const int c = c0 + cl, r = r0 + rl;
+          if (tile_ok[rl][cl] && r < V.rows && c < C) {
+            const __nv_bfloat16 b = __float2bfloat16(tile[rl][cl]);
+            for (int q = 0; q < pi.n_copies; ++q) {
+              // flag bit0: consumers fetch this operand from its owner by TMA (pull-fused GEMM), so the
+              // transposed copy is NOT broadcast; only the owner's own buffer is refreshed
+              if ((V.reserved & 1) && pi.copy_delta[q] != 0) continue;
+              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(V.w_t) + pi.copy_delta[q]);
+              dst[static_cast<long long>(c) * V.ld_t + r] = b;
+            }
           }
         }
       }
@@ -509,7 +539,7 @@ static int build_table(VarTable* vt, const TtdVarDesc* vars, int nvars, long lon
       if (r_hi > R) r_hi = R;
       if (r_lo > r_hi) r_lo = r_hi;
     }
-    const int tr0 = static_cast<int>(r_lo / kTile), tr1 = static_cast<int>((r_hi + kTile - 1) / kTile);
+    const int tr0 = static_cast<int>(r_lo / kTileR), tr1 = static_cast<int>((r_hi + kTileR - 1) / kTileR);
     const int tc = static_cast<int>((C + kTile - 1) / kTile);
     vt->tile_row0[i] = tr0;
     acc += (r_hi > r_lo ? (tr1 - tr0) : 0) * tc;
