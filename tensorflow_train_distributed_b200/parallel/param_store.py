@@ -67,7 +67,10 @@ class GpuParamStore:
         # GEMM fetches each k-block from its owner by TMA over NVLink instead
         self.pull_fused_first = bool(pull_fused_first and comm is not None)
         import os as _os
-        self.use_multicast = _os.environ.get("TTD_NVLS", "1") != "0"
+        # NVLS (in-switch reduction / replication) pays off once several peers are involved; with two GPUs plain
+        # peer loads and stores are ~1.6x faster (measured: 533 vs 850 us for the 73.6 M-parameter push)
+        nvls_env = _os.environ.get("TTD_NVLS", "auto")
+        self.use_multicast = (nvls_env == "1") or (nvls_env == "auto" and comm is not None and comm.world_size > 2)
         self.lib = N.load()
         self.world = comm.world_size if comm is not None else 1
         self.rank = comm.rank if comm is not None else 0
