@@ -65,8 +65,12 @@ __global__ void __launch_bounds__(256) prep_input_kernel(const float* __restrict
                                                          const long long* __restrict__ labels_pool,
                                                          long long* __restrict__ labels_out, int pool_batches,
                                                          const unsigned long long* __restrict__ step_ptr,
-                                                         float* __restrict__ xf) {
+                                                         float* __restrict__ xf, int use_pdl) {
   __shared__ float tile[32][33];
+  if (use_pdl) {  // programmatic dependent launch: started early, may not touch memory before this point
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b0 = blockIdx.y * 32, f0 = blockIdx.x * 32;
   if (pool_batches > 1 && step_ptr != nullptr) {
@@ -121,15 +125,32 @@ extern "C" int ttd_softmax_xent(const float* logits, int64_t ldl, const int64_t*
 extern "C" int ttd_prep_input(const float* x, int32_t B, int32_t F, void* xb, int64_t ldx, void* xT, int64_t ldt,
                               const int64_t* labels_pool, int64_t* labels_out, int32_t pool_batches,
                               const uint64_t* step_ptr, float* xf, void* stream) {
+  return ttd_prep_input_ex(x, B, F, xb, ldx, xT, ldt, labels_pool, labels_out, pool_batches, step_ptr, xf, 0, stream);
+}
+
+extern "C" int ttd_prep_input_ex(const float* x, int32_t B, int32_t F, void* xb, int64_t ldx, void* xT, int64_t ldt,
+                                 const int64_t* labels_pool, int64_t* labels_out, int32_t pool_batches,
+                                 const uint64_t* step_ptr, float* xf, uint32_t flags, void* stream) {
   if (B < 1 || F < 1) {
     set_error("ttd_prep_input: empty problem %dx%d", B, F);
     return -1;
   }
-  dim3 grid((F + 31) / 32, (B + 31) / 32);
-  prep_input_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      x, B, F, static_cast<__nv_bfloat16*>(xb), ldx, static_cast<__nv_bfloat16*>(xT), ldt,
-      reinterpret_cast<const long long*>(labels_pool), reinterpret_cast<long long*>(labels_out), pool_batches,
-      reinterpret_cast<const unsigned long long*>(step_ptr), xf);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((F + 31) / 32, (B + 31) / 32);
+  cfg.blockDim = dim3(256);
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  const int use_pdl = (flags & 1u) ? 1 : 0;
+  if (use_pdl) {
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  TTD_CUDA(cudaLaunchKernelEx(&cfg, prep_input_kernel, x, B, F, static_cast<__nv_bfloat16*>(xb), static_cast<long long>(ldx),
+                              static_cast<__nv_bfloat16*>(xT), static_cast<long long>(ldt),
+                              reinterpret_cast<const long long*>(labels_pool), reinterpret_cast<long long*>(labels_out),
+                              pool_batches, reinterpret_cast<const unsigned long long*>(step_ptr), xf, use_pdl));
   TTD_CUDA(cudaGetLastError());
   g_launch_count.fetch_add(1);
   return 0;

@@ -183,6 +183,10 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
                                                     float* __restrict__ ema, const __grid_constant__ PeerInfo pi,
                                                     long long lo, long long hi, TtdHyper h, TtdStepState* st,
                                                     int bump_global_step, unsigned long long seed) {
+  if (MODE == kUpdate && (bump_global_step & 2)) {  // bit1: programmatic dependent launch
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  }
   __shared__ float tile[kTileR][kTile + 1];
   __shared__ unsigned char tile_ok[kTileR][kTile + 1];
   __shared__ float s_lr, s_ema_d;
@@ -504,7 +508,7 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
         const unsigned long long old =
             atomicAdd_system(reinterpret_cast<unsigned long long*>(&pi.state0->global_step), 1ull);
         if (pi.state0 != st) st->global_step = static_cast<long long>(old) + 1;
-      } else if (bump_global_step) {
+      } else if (bump_global_step & 1) {
         st->global_step += 1;
       }
       st->local_step += 1;
@@ -625,9 +629,19 @@ extern "C" int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars, in
     }
     grid = peers->grid;
   }
-  param_kernel<kUpdate><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(vt, w, ema, pi, lo, hi, *hyper, state,
-                                                                            bump_global_step, 0);
-  TTD_CUDA(cudaGetLastError());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(grid));
+  cfg.blockDim = dim3(256);
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  if (bump_global_step & 2) {  // PDL: overlap this launch with the tail of the last wgrad kernel
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  TTD_CUDA(cudaLaunchKernelEx(&cfg, param_kernel<kUpdate>, vt, w, ema, pi, static_cast<long long>(lo),
+                              static_cast<long long>(hi), *hyper, state, static_cast<int>(bump_global_step), 0ull));
   g_launch_count.fetch_add(1);
   return 0;
 }

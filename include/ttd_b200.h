@@ -85,6 +85,10 @@ int ttd_softmax_xent(const float* logits, int64_t ldl, const int64_t* labels, in
 int ttd_prep_input(const float* x, int32_t B, int32_t F, void* xb, int64_t ldx, void* xT, int64_t ldt,
                    const int64_t* labels_pool, int64_t* labels_out, int32_t pool_batches,
                    const uint64_t* step_ptr, float* xf /* optional fp32 copy [B, F] of the staged batch */, void* stream);
+/* Same with launch flags: bit0 = programmatic dependent launch (overlaps the previous kernel's tail). */
+int ttd_prep_input_ex(const float* x, int32_t B, int32_t F, void* xb, int64_t ldx, void* xT, int64_t ldt,
+                      const int64_t* labels_pool, int64_t* labels_out, int32_t pool_batches,
+                      const uint64_t* step_ptr, float* xf, uint32_t flags, void* stream);
 
 /* ---- parameter store: variable table ------------------------------------------------------ */
 /* One entry per dense layer group: kernel [rows, cols] immediately followed by bias [cols] in the
@@ -143,7 +147,8 @@ typedef struct TtdPeers {
 /* Fused gradient push over the flat range [lo, hi) owned by the caller:
  *   g = grad_scale * sum_r grads[r][i]  (+ L1/L2 term)   lr from state->global_step (staircase decay)
  *   w -= lr*g ; ema -= (1-d)(ema-w) ; bf16 copies refreshed on every replica in `peers`
- *   last CTA: ++global_step (if bump_global_step), ++local_step, metrics_out <- metrics_acc <- 0.
+ *   last CTA: ++global_step (if bump_global_step bit0), ++local_step, metrics_out <- metrics_acc <- 0.
+ *   bump_global_step bit1: launch with programmatic dependent launch.
  * Reference :136-140 (lr), :150-152 (apply + global_step), :153-161 (EMA), :50-55 (regulariser),
  * :144-148 (SyncReplicasOptimizer mean-of-N aggregation when n_grads > 1). */
 int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars_host, int nvars, int64_t lo, int64_t hi,

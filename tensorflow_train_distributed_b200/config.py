@@ -92,7 +92,7 @@ class TrainConfig:
     dataset_size: int = 55000  # size of the TF train split
     prefetch: int = 0  # >0: background reader threads (README "ReadByQueue" variant)
     cuda_graph: bool = True
-    pdl: bool = False
+    pdl: bool = True  # programmatic dependent launch between the kernels of a step
     pull_fused: bool = True  # sync multi-GPU: fetch W1 from its owners inside the first GEMM (K3) instead of broadcasting it
     write_events: bool = True
     inject_fault: str = ""  # "step=N,rank=R" test hook (kill -> resume)

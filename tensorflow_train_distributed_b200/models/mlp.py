@@ -111,9 +111,9 @@ class GpuMlp:
             pass
         elif self.x_pool is not None:
             gemm.prep_input(self.x_pool, self.a[0], self.aT[0], labels_pool=self.labels_pool, labels_out=self.labels,
-                            step_ptr=step_ptr)
+                            step_ptr=step_ptr, pdl=self.pdl)
         else:
-            gemm.prep_input(self.x, self.a[0], self.aT[0])
+            gemm.prep_input(self.x, self.a[0], self.aT[0], pdl=self.pdl)
         n += 1 if self.feed_input else 0
         return n + self.launch_forward() + self.launch_backward()
 
@@ -135,7 +135,7 @@ class GpuMlp:
         """sync: fwd/bwd + the fused push (aggregate of all replicas). async: pull + fwd/bwd + atomic push."""
         if sync:
             n = self.launch_forward_backward()
-            self.store.apply_update(bump_global_step)
+            self.store.apply_update(bump_global_step, pdl=self.pdl)
             return n + 1
         self.store.async_pull()
         n = self.launch_forward_backward()

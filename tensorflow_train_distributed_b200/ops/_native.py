@@ -157,6 +157,9 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.ttd_prep_input.restype = C.c_int
     lib.ttd_prep_input.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
                                    C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ttd_prep_input_ex.restype = C.c_int
+    lib.ttd_prep_input_ex.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                      C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
     lib.ttd_init_params.restype = C.c_int
     lib.ttd_init_params.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(VarDesc), C.c_int, C.c_uint64, C.c_void_p]
     lib.ttd_refresh_copies.restype = C.c_int

@@ -98,7 +98,7 @@ def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, C_: int, dlogits: O
 
 def prep_input(x: torch.Tensor, xb: Optional[torch.Tensor], xT: Optional[torch.Tensor], *,
                labels_pool: Optional[torch.Tensor] = None, labels_out: Optional[torch.Tensor] = None,
-               step_ptr: Optional[int] = None, xf: Optional[torch.Tensor] = None) -> None:
+               step_ptr: Optional[int] = None, xf: Optional[torch.Tensor] = None, pdl: bool = False) -> None:
     """Stage one fp32 batch as bf16 (+ transposed). ``x`` is [B, F], or a device-resident pool [P, B, F] from
     which batch ``*step_ptr % P`` is taken (its labels go to ``labels_out``)."""
     lib = N.load()
@@ -108,7 +108,7 @@ def prep_input(x: torch.Tensor, xb: Optional[torch.Tensor], xT: Optional[torch.T
         pool, B, F = x.shape
     else:
         B, F = x.shape
-    rc = lib.ttd_prep_input(x.data_ptr(), B, F, N.ptr(xb), _ld(xb) if xb is not None else 0,
-                            N.ptr(xT), _ld(xT) if xT is not None else 0, N.ptr(labels_pool), N.ptr(labels_out),
-                            pool, step_ptr, N.ptr(xf), N.cur_stream())
+    rc = lib.ttd_prep_input_ex(x.data_ptr(), B, F, N.ptr(xb), _ld(xb) if xb is not None else 0,
+                               N.ptr(xT), _ld(xT) if xT is not None else 0, N.ptr(labels_pool), N.ptr(labels_out),
+                               pool, step_ptr, N.ptr(xf), 1 if pdl else 0, N.cur_stream())
     N.check(rc, "ttd_prep_input")

@@ -231,12 +231,13 @@ class GpuParamStore:
         N.check(self.lib.ttd_refresh_copies(self.w.data_ptr(), self.vars, self.nvars, N.cur_stream()),
                 "ttd_refresh_copies")
 
-    def apply_update(self, bump_global_step: bool = True) -> None:
+    def apply_update(self, bump_global_step: bool = True, pdl: bool = False) -> None:
         """The fused push: reduce (all replicas) -> L2 -> SGD -> EMA -> refresh copies (all replicas)."""
         ema_ptr = self.ema.data_ptr() if self.hyper.ema_decay > 0 else None
         N.check(self.lib.ttd_apply_update(self.w.data_ptr(), ema_ptr, self.vars, self.nvars, self.lo, self.hi,
                                           C.byref(self._hyper_native), C.byref(self._peers), self.state_ptr,
-                                          1 if bump_global_step else 0, N.cur_stream()), "ttd_apply_update")
+                                          (1 if bump_global_step else 0) | (2 if pdl else 0), N.cur_stream()),
+                "ttd_apply_update")
 
     def async_pull(self) -> None:
         """M1 of the async step: fetch every owner's master over NVLink into the local compute copies."""
