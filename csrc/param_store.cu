@@ -306,6 +306,9 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
           if (use_ema) *reinterpret_cast<float4*>(ema + idx) = make_float4(nv[0], nv[1], nv[2], nv[3]);
           if (V.bias_c != nullptr && r == V.rows)
             broadcast_store<float4>(pi, V.bias_c + c, make_float4(val[0], val[1], val[2], val[3]), false);
+          if (V.w_f32 != nullptr && r < V.rows)  // fp32 compute copy for the fused MLP tail
+            broadcast_store<float4>(pi, V.w_f32 + static_cast<long long>(r) * V.ld_f32 + c,
+                                    make_float4(val[0], val[1], val[2], val[3]), false);
         }
         // TF-layout bf16 copy: neighbouring threads pair up so that the even one issues a 16-byte store
         {
@@ -327,8 +330,27 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
           tile_ok[rl][4 * cg + i] = ok ? 1 : 0;
         }
       }
+      if (V.w_t != nullptr || V.wt_f32 != nullptr) __syncthreads();
+      if (V.wt_f32 != nullptr) {  // transposed fp32 copy: column tid/8, eight rows at 8*(tid%8)
+        const int cl = threadIdx.x >> 3, rg = threadIdx.x & 7;
+        const int cc = c0 + cl, rr0 = r0 + 8 * rg;
+        if (cc < C) {
+          float* dst = V.wt_f32 + static_cast<long long>(cc) * V.ld_tf32 + rr0;
+          bool all_ok = rr0 + 7 < V.rows;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) all_ok = all_ok && tile_ok[8 * rg + i][cl];
+          if (all_ok) {
+            broadcast_store<float4>(pi, dst, make_float4(tile[8 * rg][cl], tile[8 * rg + 1][cl], tile[8 * rg + 2][cl], tile[8 * rg + 3][cl]), false);
+            broadcast_store<float4>(pi, dst + 4, make_float4(tile[8 * rg + 4][cl], tile[8 * rg + 5][cl], tile[8 * rg + 6][cl], tile[8 * rg + 7][cl]), false);
+          } else {
+            for (int i = 0; i < 8; ++i)
+              if (tile_ok[8 * rg + i][cl] && rr0 + i < V.rows)
+                for (int q = 0; q < pi.n_copies; ++q)
+                  *reinterpret_cast<float*>(reinterpret_cast<char*>(dst + i) + pi.copy_delta[q]) = tile[8 * rg + i][cl];
+          }
+        }
+      }
       if (V.w_t != nullptr) {
-        __syncthreads();
         {  // thread -> column tid/8, eight rows at 8*(tid%8): one 16-byte store of 8 bf16
           const int cl = threadIdx.x >> 3, rg = threadIdx.x & 7;
           const int cc = c0 + cl, rr0 = r0 + 8 * rg;
@@ -449,6 +471,11 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
             dst[c] = val;
           }
         }
+        if (MODE != kAsyncPush && V.w_f32 != nullptr && r < V.rows) {
+          for (int q = 0; q < pi.n_copies; ++q)
+            *reinterpret_cast<float*>(reinterpret_cast<char*>(V.w_f32 + static_cast<long long>(r) * V.ld_f32 + c) +
+                                      pi.copy_delta[q]) = val;
+        }
         if (MODE != kAsyncPush && V.w_rm != nullptr && r < V.rows) {
           const __nv_bfloat16 b = __float2bfloat16(val);
           for (int q = 0; q < pi.n_copies; ++q) {
@@ -460,8 +487,22 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
       tile[rl][lane] = val;
       tile_ok[rl][lane] = (ok && MODE != kAsyncPush) ? 1 : 0;
     }
+    if (V.w_t != nullptr || V.wt_f32 != nullptr) __syncthreads();
+    if (V.wt_f32 != nullptr) {
+#pragma unroll
+      for (int half = 0; half < kTileR / 32; ++half) {
+#pragma unroll
+        for (int cc = 0; cc < kTile / 8; ++cc) {
+          const int cl = warp + 8 * cc, rl = lane + 32 * half;
+          const int c = c0 + cl, r = r0 + rl;
+          if (tile_ok[rl][cl] && r < V.rows && c < C)
+            for (int q = 0; q < pi.n_copies; ++q)
+              *reinterpret_cast<float*>(reinterpret_cast<char*>(V.wt_f32 + static_cast<long long>(c) * V.ld_tf32 + r) +
+                                        pi.copy_delta[q]) = tile[rl][cl];
+        }
+      }
+    }
     if (V.w_t != nullptr) {
-      __syncthreads();
 #pragma unroll
       for (int half = 0; half < kTileR / 32; ++half) {
 #pragma unroll

@@ -12,7 +12,7 @@
 // The scratch. `g_static_scratch` below is 8 KiB per GPU, resident from the moment the library is
 // loaded on that GPU until the process exits:
 //     bytes    0..255   completion counter of the launch in flight (must be zero when a launch starts)
-//     bytes  256..4351  variable table, at most kStaticMaxVars (64) groups of 64 bytes
+//     bytes  256..6399  variable table, at most kStaticMaxVars (64) groups of 96 bytes
 // The limit is therefore 64 variable groups per call; a call with more is refused with an error text,
 // nothing is launched.
 //
@@ -118,6 +118,8 @@ __global__ void __launch_bounds__(256) update_static_kernel(unsigned char* __res
         ema[idx] = s - (1.0f - ema_d) * (s - val);
       }
       if (r == V.rows && V.bias_c != nullptr) V.bias_c[c] = val;
+      if (r < V.rows && V.w_f32 != nullptr) V.w_f32[static_cast<long long>(r) * V.ld_f32 + c] = val;
+      if (r < V.rows && V.wt_f32 != nullptr) V.wt_f32[static_cast<long long>(c) * V.ld_tf32 + r] = val;
       if (r < V.rows) {
         const __nv_bfloat16 bv = __float2bfloat16(val);
         if (V.w_rm != nullptr) static_cast<__nv_bfloat16*>(V.w_rm)[static_cast<long long>(r) * V.ld_rm + c] = bv;

@@ -101,6 +101,8 @@ typedef struct TtdVarDesc {
   void* w_rm; int64_t ld_rm;  /* bf16 [rows+1, ld_rm] compute copy, TF layout (dgrad B operand) or NULL */
   void* w_t;  int64_t ld_t;   /* bf16 [cols, ld_t]   transposed compute copy (fwd B operand) or NULL */
   float* bias_c;              /* fp32 [cols] compute copy of the bias (what the forward epilogue reads) or NULL */
+  float* w_f32; int64_t ld_f32;   /* fp32 [rows, ld_f32] compute copy, TF layout (fused MLP tail) or NULL */
+  float* wt_f32; int64_t ld_tf32; /* fp32 [cols, ld_tf32] transposed compute copy (fused MLP tail) or NULL */
 } TtdVarDesc;
 
 typedef struct TtdHyper {
@@ -178,6 +180,44 @@ int ttd_async_push(float* w, const float* grads, const TtdVarDesc* vars_host, in
  * ordering recipe: 0 volatile, 1 fence+relaxed, 2 release/acquire, 3 atomicExch, 4 red.release. */
 int ttd_diag_pingpong(uint32_t* mine, uint32_t* theirs, int rank, int iters, int variant,
                       unsigned long long* out_ns, void* stream);
+
+/* ---- fused MLP tail ---------------------------------------------------------------------------------- */
+/* Every layer behind the first — forward, softmax cross-entropy, dgrad chain and all weight gradients — in ONE
+ * launch on a thread-block cluster (fp32 CUDA-core register tiles; phase boundaries are cluster barriers).
+ * Reference semantics: :54-61 (layers), :80-82 (loss), :96/:125 (accuracy), :152 (gradients).
+ * Leading dimensions are multiples of 4 floats; buffers are zero-initialised and padded as stated. */
+#define TTD_TAIL_MAX_LAYERS 6
+typedef struct TtdTailLayer {
+  int32_t in, out;
+  int32_t act_kind;          /* TTD_ACT_* applied to this layer's output (ignored for the last layer) */
+  float drop_rate;           /* dropout on this layer's output (ignored for the last layer) */
+  uint32_t layer_id;         /* dropout RNG stream */
+  int32_t reserved;
+  const float* w;  int64_t ld_w;    /* fp32 [pad4(in)][ld_w], TF layout */
+  const float* wt; int64_t ld_wt;   /* fp32 [pad4(out)][ld_wt], transposed */
+  const float* bias;                /* fp32 [out] */
+  float* dw;                        /* fp32 [in+1][out] -> flat gradient buffer (row `in` = bias gradient) */
+  float* act;  int64_t ld_act;      /* fp32 [B][ld_act] post-dropout activation; logits for the last layer */
+  float* actT; int64_t ld_actT;     /* fp32 [pad4(out+1)][ld_actT] transposed, row `out` all ones (hidden layers) */
+  float* dz;   int64_t ld_dz;       /* fp32 [pad4(B)][ld_dz] gradient w.r.t. this layer's pre-activation */
+} TtdTailLayer;
+typedef struct TtdTailDesc {
+  int32_t B, n_layers;
+  int32_t cluster;           /* CTAs in the cluster: 0 = 8 (portable maximum), up to 16 */
+  int32_t in_act_kind;       /* activation / dropout of the tensor feeding the tail (the first layer's output) */
+  float in_drop_rate;
+  uint32_t in_layer_id;
+  const void* a_in;  int64_t ld_a_in;   /* bf16 [B][ld_a_in] input activations (post-dropout) */
+  const void* a_inT; int64_t ld_a_inT;  /* bf16 [in0+1][ld_a_inT] transposed, last row all ones */
+  void* dz_in;  int64_t ld_dz_in;       /* out: bf16 [B][ld_dz_in] gradient w.r.t. the first layer's pre-activation */
+  void* dz_inT; int64_t ld_dz_inT;      /* out: bf16 [in0][ld_dz_inT] the same, transposed */
+  const int64_t* labels;                /* int64 [B] */
+  float* metrics;                       /* float[2]: += mean loss, += accuracy */
+  const uint64_t* step_ptr;             /* local step (dropout RNG) */
+  TtdTailLayer layer[TTD_TAIL_MAX_LAYERS];
+} TtdTailDesc;
+/* flags bit0: programmatic dependent launch */
+int ttd_mlp_tail(const TtdTailDesc* desc_host, uint64_t seed, uint32_t flags, void* stream);
 
 /* ---- LeNet-5 convolution stages (BASELINE config 5; the reference itself has no CNN) --------------------- */
 /* One stage = conv KHxKW stride 1 (SAME or VALID) + bias + activation + 2x2 max-pool, NHWC fp32 activations.

@@ -27,6 +27,25 @@ def _pad8(n: int) -> int:
     return -(-n // 8) * 8
 
 
+def _pad4(n: int) -> int:
+    return -(-n // 4) * 4
+
+
+TAIL_MAX_WIDTH = 256   # layers wider than this go through the tcgen05 GEMM, not the fused tail
+TAIL_MAX_BATCH = 256
+
+
+def tail_groups(layer_sizes: Sequence[int], batch: int, first_group: int = 0, enabled: bool = True):
+    """Indices (into the layout's groups) of the dense layers the fused tail kernel takes over: every layer after
+    the first one of the stack, provided all of them are narrow (their operands then live in L1/L2 and the chain
+    is launch-latency bound). Returns () when the tail does not apply."""
+    sizes = list(layer_sizes)
+    n = len(sizes)
+    if not enabled or n < 2 or n - 1 > N.TAIL_MAX_LAYERS or batch > TAIL_MAX_BATCH or max(sizes) > TAIL_MAX_WIDTH:
+        return ()
+    return tuple(range(first_group + 1, first_group + n))
+
+
 class GpuMlp:
     def __init__(self, store: GpuParamStore, batch: int, *, activation: str = "elu", dropout_rate: float = 0.01,
                  seed: int = 0, pdl: bool = False, keep_logits: bool = False, first_group: int = 0,
@@ -62,7 +81,10 @@ class GpuMlp:
         self.logits = torch.zeros(B, _pad8(sizes[-1]), device=dev, dtype=torch.float32) if keep_logits else None
         self.x_pool: Optional[torch.Tensor] = None
         self.labels_pool: Optional[torch.Tensor] = None
+        self.use_tail = all((first_group + l) in store.tail_groups for l in range(1, self.L)) and self.L >= 2
         self._build_descs()
+        if self.use_tail:
+            self._build_tail()
 
     def set_device_dataset(self, x_pool: Optional[torch.Tensor], labels_pool: Optional[torch.Tensor]) -> None:
         """Train from a device-resident pool [P, B, F] / [P, B]: batch ``local_step % P`` is picked on the
@@ -77,6 +99,8 @@ class GpuMlp:
         s, B, sz, g0 = self.store, self.B, self.sizes, self.g0
         self.fwd_descs, self.bwd_descs = [], []
         for l in range(1, self.L + 1):
+            if self.use_tail and l >= 2:
+                break  # layers 2..L belong to the fused tail kernel
             last = l == self.L
             kw = dict(bias=s.bias(g0 + l - 1), layer_id=l)
             if last:
@@ -91,6 +115,8 @@ class GpuMlp:
                                    drop_rate=self.drop, out=self.a[l], outT=self.aT[l], **kw)
             self.fwd_descs.append(d)
         for l in range(self.L, 0, -1):
+            if self.use_tail and l >= 2:
+                continue
             grp = [gemm.make_desc(self.aT[l - 1], self.dzT[l - 1], sz[l - 1] + 1, sz[l], B, N.EPI_WGRAD,
                                   outf=s.grad_matrix(g0 + l - 1), scale=1.0)]
             if l > 1:
@@ -101,6 +127,52 @@ class GpuMlp:
                 grp.append(gemm.make_desc(self.dz[0], s.w_rm[g0], B, sz[0], sz[1], N.EPI_DGRAD, act=self.act,
                                           drop_rate=0.0, layer_id=0, aux=self.a[0], out=self.dz0))
             self.bwd_descs.append(grp)
+
+    # -------------------------------------------------------------------------------------------
+    def _build_tail(self) -> None:
+        """Descriptor + fp32 scratch of the fused tail (layers 2..L of this stack): see csrc/mlp_tail.cu."""
+        s, B, sz, g0 = self.store, self.B, self.sizes, self.g0
+        dev = s.device
+        d = N.TailDesc()
+        d.B, d.n_layers, d.cluster = B, self.L - 1, 0
+        d.in_act_kind, d.in_drop_rate, d.in_layer_id = self.act, self.drop, 1
+        d.a_in, d.ld_a_in = self.a[1].data_ptr(), self.a[1].stride(0)
+        d.a_inT, d.ld_a_inT = self.aT[1].data_ptr(), self.aT[1].stride(0)
+        d.dz_in, d.ld_dz_in = self.dz[0].data_ptr(), self.dz[0].stride(0)
+        d.dz_inT, d.ld_dz_inT = self.dzT[0].data_ptr(), self.dzT[0].stride(0)
+        d.labels = self.labels.data_ptr()
+        d.metrics = s.metrics_acc_ptr
+        d.step_ptr = s.local_step_ptr
+        self._tail_bufs = []
+        f32 = dict(device=dev, dtype=torch.float32)
+        for j in range(self.L - 1):
+            l = j + 2  # 1-based layer number inside this stack
+            gi = g0 + l - 1
+            y = d.layer[j]
+            y.in_, y.out = sz[l - 1], sz[l]
+            y.act_kind, y.drop_rate, y.layer_id = self.act, self.drop, l
+            y.w, y.ld_w = s.w_f32[gi].data_ptr(), s.w_f32[gi].stride(0)
+            y.wt, y.ld_wt = s.wt_f32[gi].data_ptr(), s.wt_f32[gi].stride(0)
+            y.bias = s.bias(gi).data_ptr()
+            y.dw = s.grad_matrix(gi).data_ptr()
+            act = torch.zeros(B, _pad4(sz[l]), **f32)
+            actT = torch.zeros(_pad4(sz[l] + 1), _pad4(B), **f32)
+            actT[sz[l], :B] = 1.0
+            dz = torch.zeros(_pad4(B), _pad4(sz[l]), **f32)
+            y.act, y.ld_act = act.data_ptr(), act.stride(0)
+            y.actT, y.ld_actT = actT.data_ptr(), actT.stride(0)
+            y.dz, y.ld_dz = dz.data_ptr(), dz.stride(0)
+            self._tail_bufs.append((act, actT, dz))
+        self._tail_desc = d
+        if self.logits is not None:  # the last layer's "activation" buffer holds the logits
+            self.logits = self._tail_bufs[-1][0]
+
+    def launch_tail(self) -> int:
+        import ctypes as C
+        lib = self.store.lib
+        N.check(lib.ttd_mlp_tail(C.byref(self._tail_desc), C.c_uint64(self.seed & (2**64 - 1)), 1 if self.pdl else 0,
+                                 N.cur_stream()), "ttd_mlp_tail")
+        return 1
 
     # -------------------------------------------------------------------------------------------
     def launch_forward_backward(self) -> int:
@@ -119,6 +191,9 @@ class GpuMlp:
 
     def launch_forward(self) -> int:
         step_ptr, n = self.store.local_step_ptr, 0
+        if self.use_tail:  # first layer on the tensor cores, everything behind it in one fused launch
+            gemm.gemm_group([self.fwd_descs[0]], seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
+            return 1 + self.launch_tail()
         for d in self.fwd_descs:
             gemm.gemm_group([d], seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
             n += 1
@@ -126,6 +201,9 @@ class GpuMlp:
 
     def launch_backward(self) -> int:
         step_ptr, n = self.store.local_step_ptr, 0
+        if self.use_tail:  # the tail already produced dz of the first layer and every other gradient
+            gemm.gemm_group(self.bwd_descs[-1], seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
+            return 1
         for grp in self.bwd_descs:
             gemm.gemm_group(grp, seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
             n += 1

@@ -53,6 +53,8 @@ class VarDesc(C.Structure):
         ("w_rm", C.c_void_p), ("ld_rm", C.c_int64),
         ("w_t", C.c_void_p), ("ld_t", C.c_int64),
         ("bias_c", C.c_void_p),
+        ("w_f32", C.c_void_p), ("ld_f32", C.c_int64),
+        ("wt_f32", C.c_void_p), ("ld_tf32", C.c_int64),
     ]
 
 
@@ -120,6 +122,31 @@ class ConvDesc(C.Structure):
                 ("KH", C.c_int32), ("KW", C.c_int32), ("same_pad", C.c_int32)]
 
 
+TAIL_MAX_LAYERS = 6
+
+
+class TailLayer(C.Structure):
+    _fields_ = [
+        ("in_", C.c_int32), ("out", C.c_int32), ("act_kind", C.c_int32), ("drop_rate", C.c_float),
+        ("layer_id", C.c_uint32), ("reserved", C.c_int32),
+        ("w", C.c_void_p), ("ld_w", C.c_int64), ("wt", C.c_void_p), ("ld_wt", C.c_int64),
+        ("bias", C.c_void_p), ("dw", C.c_void_p),
+        ("act", C.c_void_p), ("ld_act", C.c_int64), ("actT", C.c_void_p), ("ld_actT", C.c_int64),
+        ("dz", C.c_void_p), ("ld_dz", C.c_int64),
+    ]
+
+
+class TailDesc(C.Structure):
+    _fields_ = [
+        ("B", C.c_int32), ("n_layers", C.c_int32), ("cluster", C.c_int32), ("in_act_kind", C.c_int32),
+        ("in_drop_rate", C.c_float), ("in_layer_id", C.c_uint32),
+        ("a_in", C.c_void_p), ("ld_a_in", C.c_int64), ("a_inT", C.c_void_p), ("ld_a_inT", C.c_int64),
+        ("dz_in", C.c_void_p), ("ld_dz_in", C.c_int64), ("dz_inT", C.c_void_p), ("ld_dz_inT", C.c_int64),
+        ("labels", C.c_void_p), ("metrics", C.c_void_p), ("step_ptr", C.c_void_p),
+        ("layer", TailLayer * TAIL_MAX_LAYERS),
+    ]
+
+
 class NativeError(RuntimeError):
     pass
 
@@ -179,6 +206,8 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.ttd_conv_pool_bwd.restype = C.c_int
     lib.ttd_conv_pool_bwd.argtypes = [C.POINTER(ConvDesc), C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
+    lib.ttd_mlp_tail.restype = C.c_int
+    lib.ttd_mlp_tail.argtypes = [C.POINTER(TailDesc), C.c_uint64, C.c_uint32, C.c_void_p]
     lib.ttd_copy_d2d.restype = C.c_int
     lib.ttd_copy_d2d.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     _lib = lib

@@ -59,8 +59,13 @@ class GpuTrainer:
         self.hyper = hyper_from_config(cfg, n_agg)
         with torch.cuda.stream(self.stream):
             lenet = cfg.model == "lenet"
+            if lenet:  # dense head = groups 2.. (fc1, fc2, output); its first layer stays on the GEMM path
+                tail = mlp_model.tail_groups([120, 84, cfg.num_classes], cfg.batch_size, 2, cfg.fused_tail)
+            else:
+                tail = mlp_model.tail_groups(cfg.layer_sizes, cfg.batch_size, 0, cfg.fused_tail)
             self.store = GpuParamStore(self.layout, self.hyper, self.device, comm=comm, need_w_rm_first=lenet,
-                                       pull_fused_first=self.sync and self.world > 1 and cfg.pull_fused and not lenet)
+                                       pull_fused_first=self.sync and self.world > 1 and cfg.pull_fused and not lenet,
+                                       tail_groups=tail)
             self.model = self._build_model()
             self._pinned_state = torch.zeros(self.RING, 8, dtype=torch.int64).pin_memory()
         self._graph: Optional[torch.cuda.CUDAGraph] = None

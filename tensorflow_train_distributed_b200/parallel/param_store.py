@@ -60,7 +60,7 @@ class Hyper:
 
 class GpuParamStore:
     def __init__(self, layout: ParamLayout, hyper: Hyper, device: torch.device, *, comm=None,
-                 need_w_rm_first: bool = False, pull_fused_first: bool = False):
+                 need_w_rm_first: bool = False, pull_fused_first: bool = False, tail_groups=()):
         """``comm`` is a :class:`~.symmetric.SymmetricComm` for multi-GPU runs (None: single GPU)."""
         self.layout, self.hyper, self.device, self.comm = layout, hyper, device, comm
         # K3: the first layer's transposed weights are not broadcast after an update; every replica's first
@@ -71,6 +71,8 @@ class GpuParamStore:
         # peer loads and stores are ~1.6x faster (measured: 533 vs 850 us for the 73.6 M-parameter push)
         nvls_env = _os.environ.get("TTD_NVLS", "auto")
         self.use_multicast = (nvls_env == "1") or (nvls_env == "auto" and comm is not None and comm.world_size > 2)
+        # groups served by the fused MLP tail kernel: fp32 compute copies (both layouts) instead of bf16 ones
+        self.tail_groups = frozenset(tail_groups)
         self.lib = N.load()
         self.world = comm.world_size if comm is not None else 1
         self.rank = comm.rank if comm is not None else 0
@@ -79,17 +81,22 @@ class GpuParamStore:
         # ---- carve one arena: grads | w | bf16 copies | fp32 bias copies | flags --------------------
         sizes = []
         for i, g in enumerate(layout.groups):
-            want_rm = need_w_rm_first or i > 0  # dgrad of the first layer is never needed (input has no grad)
-            sizes.append((g.rows * _pad8(g.cols) if want_rm else 0, g.cols * _pad8(g.rows), g.cols))
+            tail = i in self.tail_groups
+            want_rm = (need_w_rm_first or i > 0) and not tail  # first-layer dgrad is never needed (input has no grad)
+            sizes.append((g.rows * _pad8(g.cols) if want_rm else 0, 0 if tail else g.cols * _pad8(g.rows), g.cols))
         bf16_elems = sum(_align(a, 128) + _align(b, 128) for a, b, _ in sizes)
         bias_elems = sum(_align(c, 64) for _, _, c in sizes)
+        f32_sizes = [(_align(g.rows, 4) * _align(g.cols, 4), _align(g.cols, 4) * _align(g.rows, 4))
+                     if i in self.tail_groups else (0, 0) for i, g in enumerate(layout.groups)]
+        f32_elems = sum(_align(a, 64) + _align(b, 64) for a, b in f32_sizes)
         o_grads = 0
         o_w = o_grads + total * 4
         o_ema = o_w + total * 4
         o_state = o_ema + total * 4
         o_bf16 = o_state + 256
         o_bias = o_bf16 + _align(bf16_elems * 2, 256)
-        o_flags = o_bias + _align(bias_elems * 4, 256)
+        o_f32 = o_bias + _align(bias_elems * 4, 256)
+        o_flags = o_f32 + _align(f32_elems * 4, 256)
         nbytes = o_flags + FLAG_SLOTS * N.MAX_PEERS * 4
         if comm is not None:
             self._arena = comm.alloc(nbytes)
@@ -104,6 +111,7 @@ class GpuParamStore:
         self.w = raw[o_w:o_w + total * 4].view(torch.float32)
         copies = raw[o_bf16:o_bf16 + bf16_elems * 2].view(torch.bfloat16)
         biases = raw[o_bias:o_bias + bias_elems * 4].view(torch.float32)
+        f32c = raw[o_f32:o_f32 + f32_elems * 4].view(torch.float32)
         self.ema = raw[o_ema:o_ema + total * 4].view(torch.float32)
         self.state = raw[o_state:o_state + 64].view(torch.int64)  # TtdStepState (64 B)
         self._off = dict(grads=o_grads, w=o_w, ema=o_ema, state=o_state)
@@ -111,6 +119,18 @@ class GpuParamStore:
         self.w_rm: List[Optional[torch.Tensor]] = []
         self.w_t: List[torch.Tensor] = []
         self.bias_c: List[torch.Tensor] = []
+        self.w_f32: List[Optional[torch.Tensor]] = []
+        self.wt_f32: List[Optional[torch.Tensor]] = []
+        foff = 0
+        for g, (fa, fb) in zip(layout.groups, f32_sizes):
+            if fa:
+                self.w_f32.append(f32c[foff:foff + fa].view(_align(g.rows, 4), _align(g.cols, 4)))
+                foff += _align(fa, 64)
+                self.wt_f32.append(f32c[foff:foff + fb].view(_align(g.cols, 4), _align(g.rows, 4)))
+                foff += _align(fb, 64)
+            else:
+                self.w_f32.append(None)
+                self.wt_f32.append(None)
         off = boff = 0
         for g, (rm, t, c) in zip(layout.groups, sizes):
             if rm:
@@ -118,20 +138,24 @@ class GpuParamStore:
                 off += _align(rm, 128)
             else:
                 self.w_rm.append(None)
-            self.w_t.append(copies[off:off + t].view(g.cols, _pad8(g.rows)))
+            self.w_t.append(copies[off:off + t].view(g.cols, _pad8(g.rows)) if t else None)
             off += _align(t, 128)
             self.bias_c.append(biases[boff:boff + c])
             boff += _align(c, 64)
 
         # ---- variable table ----------------------------------------------------------------------
         descs = []
-        for g, rm, t, b in zip(layout.groups, self.w_rm, self.w_t, self.bias_c):
+        for g, rm, t, b, wf, wtf in zip(layout.groups, self.w_rm, self.w_t, self.bias_c, self.w_f32, self.wt_f32):
             v = N.VarDesc()
             v.offset, v.rows, v.cols = g.offset, g.rows, g.cols
             v.regularize = 1 if g.regularize else 0
             if rm is not None:
                 v.w_rm, v.ld_rm = rm.data_ptr(), rm.stride(0)
-            v.w_t, v.ld_t = t.data_ptr(), t.stride(0)
+            if t is not None:
+                v.w_t, v.ld_t = t.data_ptr(), t.stride(0)
+            if wf is not None:
+                v.w_f32, v.ld_f32 = wf.data_ptr(), wf.stride(0)
+                v.wt_f32, v.ld_tf32 = wtf.data_ptr(), wtf.stride(0)
             v.bias_c = b.data_ptr()
             if self.pull_fused_first and not descs:
                 v.reserved = 1

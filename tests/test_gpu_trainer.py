@@ -30,11 +30,12 @@ def _torch_reference(vars_, x, y, sizes, act="elu"):
     return loss.item(), (h.argmax(1) == y).float().mean().item(), ws, bs
 
 
-@pytest.mark.parametrize("act", ["elu", "relu"])
-def test_step_gradients_match_autograd(act):
+@pytest.mark.parametrize("act,fused_tail", [("elu", True), ("relu", True), ("elu", False), ("relu", False)])
+def test_step_gradients_match_autograd(act, fused_tail):
+    """Both back ends of the narrow layers: the fused cluster kernel and one tcgen05 GEMM per layer."""
     from tensorflow_train_distributed_b200.data import synthetic_mnist
     from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
-    cfg = _cfg(dropout_rate=0.0, cuda_graph=False, activation=act)
+    cfg = _cfg(dropout_rate=0.0, cuda_graph=False, activation=act, fused_tail=fused_tail)
     tr = GpuTrainer(cfg)
     tr.initialize()
     ds = synthetic_mnist(1024, seed=5)
@@ -67,7 +68,11 @@ def test_graph_replay_equals_eager_and_learns():
     a = GpuTrainer(_cfg(cuda_graph=True))
     b = GpuTrainer(_cfg(cuda_graph=False))
     a.initialize(), b.initialize()
-    assert a.launches_per_step == 12  # prep + 5 fwd + 5 bwd + update for the reference model
+    assert a.launches_per_step == 5   # prep + first-layer fwd + fused tail + first-layer wgrad + update
+    c = GpuTrainer(_cfg(cuda_graph=False, fused_tail=False))
+    c.initialize()
+    assert c.launches_per_step == 12  # prep + 5 fwd + 5 bwd + update when every layer is its own GEMM
+    c.close()
     la = lb = None
     first = None
     for _ in range(60):
@@ -194,3 +199,27 @@ def test_lenet_gradients_match_autograd_and_it_learns():
         first = first or last.loss
     assert last.loss < 0.6 * first and last.global_step == 80
     tr.close()
+
+
+def test_fused_tail_follows_the_per_layer_path_with_dropout():
+    """Same seeds, dropout on: the cluster kernel and the per-layer GEMM path draw identical masks, so the two
+    trajectories stay together (fp32 tail vs bf16 GEMMs: small numeric drift only)."""
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    ds1, ds2 = synthetic_mnist(4096, seed=6), synthetic_mnist(4096, seed=6)
+    a = GpuTrainer(_cfg(dropout_rate=0.2, fused_tail=True))
+    b = GpuTrainer(_cfg(dropout_rate=0.2, fused_tail=False))
+    a.initialize(), b.initialize()
+    for i in range(40):
+        xa, ya = ds1.next_batch(128)
+        xb, yb = ds2.next_batch(128)
+        va, vb = a.train_step(xa, ya), b.train_step(xb, yb)
+        if i == 0:
+            assert abs(va.loss - vb.loss) < 2e-2 * max(1.0, vb.loss)
+    assert va.global_step == vb.global_step == 40
+    assert abs(va.loss - vb.loss) < 0.15 * max(vb.loss, 0.2)
+    wa, wb = a.export_variables(), b.export_variables()
+    for k in ("hidden1/kernel", "hidden3/kernel", "output/bias"):
+        cos = float(np.dot(wa[k].ravel(), wb[k].ravel()) / (np.linalg.norm(wa[k]) * np.linalg.norm(wb[k]) + 1e-12))
+        assert cos > 0.999, (k, cos)
+    a.close(), b.close()
