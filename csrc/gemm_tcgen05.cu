@@ -106,6 +106,222 @@ __device__ __forceinline__ void store_row_chunk(const GemmProblem& P, int m, int
   }
 }
 
+// Everything the four epilogue warps do with a finished accumulator tile (rows m0.., columns nbase.. of problem P):
+// shared by the one-tile-per-CTA kernel and by the chain kernel, which walks a list of dependent problems.
+struct EpiCtx {
+  uint32_t seed_lo, seed_hi;
+  const unsigned long long* step_ptr;
+  uint8_t* smem;  // idle pipeline stages, reused as a staging patch by the wgrad epilogue
+};
+
+__device__ __forceinline__ void run_epilogue(const GemmProblem& P, const EpiCtx& E, uint32_t tmem_base, int m0,
+                                             int nbase, int warp, int lane) {
+  // ===================== epilogue: TMEM -> registers -> global =====================
+  const int quad = warp & 3;  // TMEM lane quadrant this warp may read
+  const int m = m0 + quad * 32 + lane;
+  const bool row_ok = m < P.M;
+  const unsigned long long step = E.step_ptr != nullptr ? *E.step_ptr : 0ull;
+  const uint32_t taddr_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+  const int nchunks = P.block_n / 16;
+  float v[16];
+
+  if (P.mode == TTD_EPI_FWD_XENT) {
+    // One thread owns one example's whole logit row (N <= block_n). Three cheap passes over TMEM.
+    const long long label = row_ok ? P.labels[m] : 0;
+    float zmax = -INFINITY, zlab = 0.0f;
+    for (int c = 0; c < nchunks; ++c) {
+      __syncwarp();
+      tmem_ld16(taddr_row + c * 16, v);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int n = c * 16 + j;
+        if (n < P.N) {
+          const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
+          zmax = fmaxf(zmax, z);
+          if (n == label) zlab = z;
+        }
+      }
+    }
+    float sum = 0.0f;
+    int greater = 0;
+    for (int c = 0; c < nchunks; ++c) {
+      __syncwarp();
+      tmem_ld16(taddr_row + c * 16, v);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int n = c * 16 + j;
+        if (n < P.N) {
+          const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
+          sum += __expf(z - zmax);
+          greater += (z > zlab) ? 1 : 0;
+        }
+      }
+    }
+    const float inv_sum = 1.0f / sum;
+    const float gscale = P.scale / static_cast<float>(P.M);
+    for (int c = 0; c < nchunks; ++c) {
+      __syncwarp();
+      tmem_ld16(taddr_row + c * 16, v);
+      float d[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int n = c * 16 + j;
+        float dz = 0.0f;
+        if (n < P.N) {
+          const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
+          if (row_ok && P.outf) P.outf[static_cast<long long>(m) * P.ldf + n] = z;
+          dz = (__expf(z - zmax) * inv_sum - (n == label ? 1.0f : 0.0f)) * gscale;
+        }
+        d[j] = dz;
+      }
+      if (row_ok) store_row_chunk(P, m, c * 16, d);
+    }
+    float loss = row_ok ? (__logf(sum) + zmax - zlab) / static_cast<float>(P.M) : 0.0f;
+    float corr = (row_ok && greater < 1) ? 1.0f / static_cast<float>(P.M) : 0.0f;
+    loss = warp_sum(loss);
+    corr = warp_sum(corr);
+    if (lane == 0 && P.metrics) {
+      atomicAdd(&P.metrics[0], loss);
+      atomicAdd(&P.metrics[1], corr);
+    }
+  } else {
+    const float keep = 1.0f - P.drop_rate;
+    const float inv_keep = 1.0f / keep;
+    const bool wide_store = P.mode == TTD_EPI_WGRAD && (P.block_n % 32) == 0 && (P.N % 4) == 0 && (P.ldf % 4) == 0 &&
+                            (reinterpret_cast<uintptr_t>(P.outf) & 15u) == 0;
+    const uint32_t drop_thresh = static_cast<uint32_t>(fminf(P.drop_rate, 1.0f) * 4294967040.0f);
+    for (int c = 0; c < nchunks; ++c) {
+      const int n0 = nbase + c * 16;
+      __syncwarp();                      // tcgen05.ld is warp-collective: reconverge before it
+      tmem_ld16(taddr_row + c * 16, v);
+      const bool live = row_ok && n0 < P.N;
+      if (P.mode == TTD_EPI_WGRAD && wide_store) {
+        // 32 rows x 32 fp32 columns per warp go through a private smem patch (the pipeline stages are idle
+        // by now) so that every global store instruction writes whole 128-byte lines of four rows instead
+        // of 16 bytes of thirty-two rows
+        float v2[16];
+        __syncwarp();
+        tmem_ld16(taddr_row + c * 16 + 16, v2);
+        float* patch = reinterpret_cast<float*>(E.smem) + (warp - 4) * (32 * 36);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          *reinterpret_cast<float4*>(patch + lane * 36 + 4 * q) =
+              make_float4(v[4 * q] * P.scale, v[4 * q + 1] * P.scale, v[4 * q + 2] * P.scale, v[4 * q + 3] * P.scale);
+          *reinterpret_cast<float4*>(patch + lane * 36 + 16 + 4 * q) =
+              make_float4(v2[4 * q] * P.scale, v2[4 * q + 1] * P.scale, v2[4 * q + 2] * P.scale, v2[4 * q + 3] * P.scale);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rl = i * 4 + (lane >> 3), c4 = (lane & 7) * 4;
+          const int mm = m0 + quad * 32 + rl, nn = n0 + c4;
+          if (mm < P.M && nn < P.N)  // N % 4 == 0 in this mode, so a float4 never straddles the edge
+            *reinterpret_cast<float4*>(P.outf + static_cast<long long>(mm) * P.ldf + nn) =
+                *reinterpret_cast<const float4*>(patch + rl * 36 + c4);
+        }
+        ++c;  // two 16-column chunks consumed
+      } else if (live && P.mode == TTD_EPI_WGRAD) {
+        float* row = P.outf + static_cast<long long>(m) * P.ldf;
+        const bool vec = ((reinterpret_cast<uintptr_t>(row + n0) & 15u) == 0) && (n0 + 16 <= P.N);
+        if (vec) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            *reinterpret_cast<float4*>(row + n0 + 4 * q) =
+                make_float4(v[4 * q] * P.scale, v[4 * q + 1] * P.scale, v[4 * q + 2] * P.scale,
+                            v[4 * q + 3] * P.scale);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (n0 + j < P.N) row[n0 + j] = v[j] * P.scale;
+        }
+      } else if (live && P.swap) {
+        // Weight-stationary orientation: this thread owns output feature f = m and the 16 columns are
+        // consecutive batch rows. All pointers keep their logical [batch, feature] meaning.
+        const int f = m;
+        const float bias_f = (P.mode == TTD_EPI_FWD && P.bias) ? P.bias[f] : 0.0f;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int b = n0 + j;
+          float r = 0.0f;
+          if (b < P.N) {
+            bool kept = true;
+            if (P.drop_rate > 0.0f) {
+              const Philox4 rnd = dropout_block(static_cast<uint32_t>(b), static_cast<uint32_t>(f >> 2), step,
+                                                P.layer_id, E.seed_lo, E.seed_hi);
+              kept = philox_pick(rnd, f & 3) >= drop_thresh;
+            }
+            if (P.mode == TTD_EPI_FWD) {
+              const float a = act_apply(v[j] + bias_f, P.act);
+              if (P.outf) P.outf[static_cast<long long>(b) * P.ldf + f] = a;
+              r = kept ? a * inv_keep : 0.0f;
+            } else {  // DGRAD
+              const float a_sv = P.aux ? __bfloat162float(P.aux[static_cast<long long>(b) * P.ldaux + f]) : 1.0f;
+              r = kept ? v[j] * inv_keep * act_grad_from_out(a_sv * keep, P.act) : 0.0f;
+            }
+          }
+          v[j] = r;
+        }
+        if (P.out != nullptr) {  // [batch, feature]: lanes are consecutive features -> coalesced
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (n0 + j < P.N) P.out[static_cast<long long>(n0 + j) * P.ldo + f] = __float2bfloat16(v[j]);
+        }
+        if (P.outT != nullptr) {  // [feature, batch]: 16 consecutive batch entries of this thread's row
+          __nv_bfloat16* row = P.outT + static_cast<long long>(f) * P.ldt;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int nb = n0 + 8 * h;
+            if (nb + 8 <= P.ldt) {
+              store_bf16x8(row + nb, v + 8 * h);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                if (nb + j < P.N) row[nb + j] = __float2bfloat16(v[8 * h + j]);
+            }
+          }
+        }
+      } else if (live) {
+        float a_saved[16];
+        if (P.mode == TTD_EPI_DGRAD && P.aux != nullptr) {
+          const __nv_bfloat16* arow = P.aux + static_cast<long long>(m) * P.ldaux;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) a_saved[j] = (n0 + j < P.N) ? __bfloat162float(arow[n0 + j]) : 0.0f;
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) a_saved[j] = 1.0f;
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          Philox4 rnd{0, 0, 0, 0};
+          if (P.drop_rate > 0.0f)
+            rnd = dropout_block(static_cast<uint32_t>(m), static_cast<uint32_t>((n0 >> 2) + q), step, P.layer_id,
+                                E.seed_lo, E.seed_hi);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int j = 4 * q + i;
+            const int n = n0 + j;
+            float r = 0.0f;
+            if (n < P.N) {
+              const bool kept = (P.drop_rate <= 0.0f) || (philox_pick(rnd, i) >= drop_thresh);
+              if (P.mode == TTD_EPI_FWD) {
+                const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
+                const float a = act_apply(z, P.act);
+                if (P.outf) P.outf[static_cast<long long>(m) * P.ldf + n] = a;
+                r = kept ? a * inv_keep : 0.0f;
+              } else {  // DGRAD
+                const float a = a_saved[j] * keep;  // undo the 1/keep scaling of the saved activation
+                r = kept ? v[j] * inv_keep * act_grad_from_out(a, P.act) : 0.0f;
+              }
+            }
+            v[j] = r;
+          }
+        }
+        store_row_chunk(P, m, n0, v);
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_constant__ GemmGroup g) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -235,211 +451,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
     }
   } else if (warp >= 4) {
     // ===================== epilogue: TMEM -> registers -> global =====================
-    const int quad = warp & 3;  // TMEM lane quadrant this warp may read
-    const int m = m0 + quad * 32 + lane;
-    const bool row_ok = m < P.M;
-    const unsigned long long step = g.step_ptr != nullptr ? *g.step_ptr : 0ull;
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
-    const uint32_t taddr_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-    const int nchunks = P.block_n / 16;
-    float v[16];
-
-    if (P.mode == TTD_EPI_FWD_XENT) {
-      // One thread owns one example's whole logit row (N <= block_n). Three cheap passes over TMEM.
-      const long long label = row_ok ? P.labels[m] : 0;
-      float zmax = -INFINITY, zlab = 0.0f;
-      for (int c = 0; c < nchunks; ++c) {
-        __syncwarp();
-        tmem_ld16(taddr_row + c * 16, v);
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int n = c * 16 + j;
-          if (n < P.N) {
-            const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
-            zmax = fmaxf(zmax, z);
-            if (n == label) zlab = z;
-          }
-        }
-      }
-      float sum = 0.0f;
-      int greater = 0;
-      for (int c = 0; c < nchunks; ++c) {
-        __syncwarp();
-        tmem_ld16(taddr_row + c * 16, v);
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int n = c * 16 + j;
-          if (n < P.N) {
-            const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
-            sum += __expf(z - zmax);
-            greater += (z > zlab) ? 1 : 0;
-          }
-        }
-      }
-      const float inv_sum = 1.0f / sum;
-      const float gscale = P.scale / static_cast<float>(P.M);
-      for (int c = 0; c < nchunks; ++c) {
-        __syncwarp();
-        tmem_ld16(taddr_row + c * 16, v);
-        float d[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int n = c * 16 + j;
-          float dz = 0.0f;
-          if (n < P.N) {
-            const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
-            if (row_ok && P.outf) P.outf[static_cast<long long>(m) * P.ldf + n] = z;
-            dz = (__expf(z - zmax) * inv_sum - (n == label ? 1.0f : 0.0f)) * gscale;
-          }
-          d[j] = dz;
-        }
-        if (row_ok) store_row_chunk(P, m, c * 16, d);
-      }
-      float loss = row_ok ? (__logf(sum) + zmax - zlab) / static_cast<float>(P.M) : 0.0f;
-      float corr = (row_ok && greater < 1) ? 1.0f / static_cast<float>(P.M) : 0.0f;
-      loss = warp_sum(loss);
-      corr = warp_sum(corr);
-      if (lane == 0 && P.metrics) {
-        atomicAdd(&P.metrics[0], loss);
-        atomicAdd(&P.metrics[1], corr);
-      }
-    } else {
-      const float keep = 1.0f - P.drop_rate;
-      const float inv_keep = 1.0f / keep;
-      const bool wide_store = P.mode == TTD_EPI_WGRAD && (P.block_n % 32) == 0 && (P.N % 4) == 0 && (P.ldf % 4) == 0 &&
-                              (reinterpret_cast<uintptr_t>(P.outf) & 15u) == 0;
-      const uint32_t drop_thresh = static_cast<uint32_t>(fminf(P.drop_rate, 1.0f) * 4294967040.0f);
-      for (int c = 0; c < nchunks; ++c) {
-        const int n0 = nbase + c * 16;
-        __syncwarp();                      // tcgen05.ld is warp-collective: reconverge before it
-        tmem_ld16(taddr_row + c * 16, v);
-        const bool live = row_ok && n0 < P.N;
-        if (P.mode == TTD_EPI_WGRAD && wide_store) {
-          // 32 rows x 32 fp32 columns per warp go through a private smem patch (the pipeline stages are idle
-          // by now) so that every global store instruction writes whole 128-byte lines of four rows instead
-          // of 16 bytes of thirty-two rows
-          float v2[16];
-          __syncwarp();
-          tmem_ld16(taddr_row + c * 16 + 16, v2);
-          float* patch = reinterpret_cast<float*>(smem) + (warp - 4) * (32 * 36);
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            *reinterpret_cast<float4*>(patch + lane * 36 + 4 * q) =
-                make_float4(v[4 * q] * P.scale, v[4 * q + 1] * P.scale, v[4 * q + 2] * P.scale, v[4 * q + 3] * P.scale);
-            *reinterpret_cast<float4*>(patch + lane * 36 + 16 + 4 * q) =
-                make_float4(v2[4 * q] * P.scale, v2[4 * q + 1] * P.scale, v2[4 * q + 2] * P.scale, v2[4 * q + 3] * P.scale);
-          }
-          __syncwarp();
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int rl = i * 4 + (lane >> 3), c4 = (lane & 7) * 4;
-            const int mm = m0 + quad * 32 + rl, nn = n0 + c4;
-            if (mm < P.M && nn < P.N)  // N % 4 == 0 in this mode, so a float4 never straddles the edge
-              *reinterpret_cast<float4*>(P.outf + static_cast<long long>(mm) * P.ldf + nn) =
-                  *reinterpret_cast<const float4*>(patch + rl * 36 + c4);
-          }
-          ++c;  // two 16-column chunks consumed
-        } else if (live && P.mode == TTD_EPI_WGRAD) {
-          float* row = P.outf + static_cast<long long>(m) * P.ldf;
-          const bool vec = ((reinterpret_cast<uintptr_t>(row + n0) & 15u) == 0) && (n0 + 16 <= P.N);
-          if (vec) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q)
-              *reinterpret_cast<float4*>(row + n0 + 4 * q) =
-                  make_float4(v[4 * q] * P.scale, v[4 * q + 1] * P.scale, v[4 * q + 2] * P.scale,
-                              v[4 * q + 3] * P.scale);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (n0 + j < P.N) row[n0 + j] = v[j] * P.scale;
-          }
-        } else if (live && P.swap) {
-          // Weight-stationary orientation: this thread owns output feature f = m and the 16 columns are
-          // consecutive batch rows. All pointers keep their logical [batch, feature] meaning.
-          const int f = m;
-          const float bias_f = (P.mode == TTD_EPI_FWD && P.bias) ? P.bias[f] : 0.0f;
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const int b = n0 + j;
-            float r = 0.0f;
-            if (b < P.N) {
-              bool kept = true;
-              if (P.drop_rate > 0.0f) {
-                const Philox4 rnd = dropout_block(static_cast<uint32_t>(b), static_cast<uint32_t>(f >> 2), step,
-                                                  P.layer_id, g.seed_lo, g.seed_hi);
-                kept = philox_pick(rnd, f & 3) >= drop_thresh;
-              }
-              if (P.mode == TTD_EPI_FWD) {
-                const float a = act_apply(v[j] + bias_f, P.act);
-                if (P.outf) P.outf[static_cast<long long>(b) * P.ldf + f] = a;
-                r = kept ? a * inv_keep : 0.0f;
-              } else {  // DGRAD
-                const float a_sv = P.aux ? __bfloat162float(P.aux[static_cast<long long>(b) * P.ldaux + f]) : 1.0f;
-                r = kept ? v[j] * inv_keep * act_grad_from_out(a_sv * keep, P.act) : 0.0f;
-              }
-            }
-            v[j] = r;
-          }
-          if (P.out != nullptr) {  // [batch, feature]: lanes are consecutive features -> coalesced
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (n0 + j < P.N) P.out[static_cast<long long>(n0 + j) * P.ldo + f] = __float2bfloat16(v[j]);
-          }
-          if (P.outT != nullptr) {  // [feature, batch]: 16 consecutive batch entries of this thread's row
-            __nv_bfloat16* row = P.outT + static_cast<long long>(f) * P.ldt;
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              const int nb = n0 + 8 * h;
-              if (nb + 8 <= P.ldt) {
-                store_bf16x8(row + nb, v + 8 * h);
-              } else {
-#pragma unroll
-                for (int j = 0; j < 8; ++j)
-                  if (nb + j < P.N) row[nb + j] = __float2bfloat16(v[8 * h + j]);
-              }
-            }
-          }
-        } else if (live) {
-          float a_saved[16];
-          if (P.mode == TTD_EPI_DGRAD && P.aux != nullptr) {
-            const __nv_bfloat16* arow = P.aux + static_cast<long long>(m) * P.ldaux;
-#pragma unroll
-            for (int j = 0; j < 16; ++j) a_saved[j] = (n0 + j < P.N) ? __bfloat162float(arow[n0 + j]) : 0.0f;
-          } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) a_saved[j] = 1.0f;
-          }
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            Philox4 rnd{0, 0, 0, 0};
-            if (P.drop_rate > 0.0f)
-              rnd = dropout_block(static_cast<uint32_t>(m), static_cast<uint32_t>((n0 >> 2) + q), step, P.layer_id,
-                                  g.seed_lo, g.seed_hi);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int j = 4 * q + i;
-              const int n = n0 + j;
-              float r = 0.0f;
-              if (n < P.N) {
-                const bool kept = (P.drop_rate <= 0.0f) || (philox_pick(rnd, i) >= drop_thresh);
-                if (P.mode == TTD_EPI_FWD) {
-                  const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
-                  const float a = act_apply(z, P.act);
-                  if (P.outf) P.outf[static_cast<long long>(m) * P.ldf + n] = a;
-                  r = kept ? a * inv_keep : 0.0f;
-                } else {  // DGRAD
-                  const float a = a_saved[j] * keep;  // undo the 1/keep scaling of the saved activation
-                  r = kept ? v[j] * inv_keep * act_grad_from_out(a, P.act) : 0.0f;
-                }
-              }
-              v[j] = r;
-            }
-          }
-          store_row_chunk(P, m, n0, v);
-        }
-      }
-    }
+    const EpiCtx E{g.seed_lo, g.seed_hi, g.step_ptr, smem};
+    run_epilogue(P, E, tmem_base, m0, nbase, warp, lane);
   }
 
   tc_fence_before();
@@ -684,6 +699,196 @@ extern "C" int ttd_gemm_group(const TtdGemmDesc* d, int count, uint64_t seed, co
   cfg.attrs = attr;
   cfg.numAttrs = nattr;
   TTD_CUDA(cudaLaunchKernelEx(&cfg, gemm_group_kernel, g));
+  g_launch_count.fetch_add(1);
+  return 0;
+}
+
+// =====================================================================================================
+// Chain kernel: a LIST of small, mutually dependent GEMM problems executed back to back by ONE CTA.
+//
+// The layers behind the first one of the reference MLP are eight dependent GEMMs (four forward, four dgrad)
+// plus four weight gradients, each far smaller than one tcgen05 tile; as separate launches they cost ~6 us
+// apiece, almost all of it launch / drain / prologue latency. Here the same tcgen05 pipeline (TMA -> smem ->
+// tcgen05.mma -> TMEM -> fused epilogue) loops over the problem list inside one CTA: a stage boundary is a
+// __syncthreads plus a generic->async proxy fence (the next stage's TMA reads what this stage's epilogue just
+// stored), not a kernel boundary. Descriptors (with their tensor maps) live in a device buffer prepared once.
+// =====================================================================================================
+namespace ttd {
+
+constexpr int kChainMaxKb = 4;      // K <= 256 per problem: every k-block of a stage is resident at once
+constexpr int kChainMaxStages = 32;
+
+struct ChainHeader {
+  int n;
+  uint32_t seed_lo, seed_hi;
+  const unsigned long long* step_ptr;
+  int use_pdl;
+};
+
+__global__ void __launch_bounds__(kThreads, 1) gemm_chain_kernel(const GemmProblem* __restrict__ probs, ChainHeader h) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;                                  // kChainMaxKb x 16 KiB
+  uint8_t* sB = smem + kChainMaxKb * kAStageBytes;     // kChainMaxKb x (256 rows x 128 B)
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sB + kChainMaxKb * 256 * kBlockK * 2);
+  uint64_t* done_bar = full_bar + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 1 && lane == 0) {
+    mbar_init(full_bar, 1);
+    mbar_init(done_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 256);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  if (h.use_pdl) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  }
+  const EpiCtx E{h.seed_lo, h.seed_hi, h.step_ptr, smem};
+  uint32_t ph = 0;
+  for (int s = 0; s < h.n; ++s) {
+    const GemmProblem& P = probs[s];
+    const int num_kb = (P.K + kBlockK - 1) / kBlockK;
+    const int b_kb_bytes = P.block_n * kBlockK * 2;
+    for (int tile = 0; tile < P.tiles_m * P.tiles_n; ++tile) {
+      const int m0 = (tile % P.tiles_m) * kBlockM, nbase = (tile / P.tiles_m) * P.block_n;
+      if (warp == 0 && lane == 0) {
+        mbar_arrive_expect_tx(full_bar, static_cast<uint32_t>(num_kb * (kAStageBytes + b_kb_bytes)));
+        for (int kb = 0; kb < num_kb; ++kb) {
+          tma_load_2d(sA + kb * kAStageBytes, &P.tma_a, full_bar, kb * kBlockK, m0);
+          tma_load_2d(sB + kb * b_kb_bytes, &P.tma_b, full_bar, kb * kBlockK, nbase);
+        }
+      } else if (warp == 1 && lane == 0) {
+        const uint32_t idesc = umma_idesc_bf16(kBlockM, static_cast<uint32_t>(P.block_n));
+        mbar_wait(full_bar, ph);
+        tc_fence_after();
+        for (int kb = 0; kb < num_kb; ++kb) {
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            const uint64_t da = umma_desc_k_sw128(smem_u32(sA + kb * kAStageBytes) + k * 32);
+            const uint64_t db = umma_desc_k_sw128(smem_u32(sB + kb * b_kb_bytes) + k * 32);
+            umma_bf16_ss(tmem_base, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+        }
+        umma_commit(done_bar);
+      } else if (warp >= 4) {
+        mbar_wait(done_bar, ph);
+        tc_fence_after();
+        run_epilogue(P, E, tmem_base, m0, nbase, warp, lane);
+        tc_fence_before();
+      }
+      // what the epilogue stored through the generic proxy is the next stage's TMA (async proxy) input
+      __threadfence();
+      fence_proxy_async();
+      __syncthreads();
+      ph ^= 1u;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256);
+  }
+}
+
+}  // namespace ttd
+
+extern "C" uint64_t ttd_gemm_chain_problem_bytes(void) { return sizeof(ttd::GemmProblem); }
+
+// Encode `count` problems (executed in order) into `device_buf` (count * ttd_gemm_chain_problem_bytes() bytes,
+// 64-byte aligned). Synchronous; do it once at set-up, not per step.
+extern "C" int ttd_gemm_chain_build(const TtdGemmDesc* d, int count, void* device_buf, void* stream) {
+  if (count < 1 || count > kChainMaxStages) {
+    set_error("ttd_gemm_chain_build: 1..%d problems, got %d", kChainMaxStages, count);
+    return -1;
+  }
+  if (reinterpret_cast<uintptr_t>(device_buf) & 63u) {
+    set_error("ttd_gemm_chain_build: the descriptor buffer must be 64-byte aligned");
+    return -1;
+  }
+  static thread_local GemmProblem host[kChainMaxStages];
+  memset(host, 0, sizeof(GemmProblem) * count);
+  for (int i = 0; i < count; ++i) {
+    const TtdGemmDesc& s = d[i];
+    GemmProblem& P = host[i];
+    const int bn = ((s.N + 15) / 16) * 16;
+    if (s.M < 1 || s.N < 1 || s.K < 1 || s.K > kChainMaxKb * kBlockK || bn > 256) {
+      set_error("ttd_gemm_chain_build: problem %d (%dx%dx%d) needs K <= %d and N <= 256", i, s.M, s.N, s.K,
+                kChainMaxKb * kBlockK);
+      return -1;
+    }
+    if (s.mode == TTD_EPI_FWD_XENT && s.labels == nullptr) {
+      set_error("ttd_gemm_chain_build: fused xent needs labels");
+      return -1;
+    }
+    int rc = make_tmap(&P.tma_a, s.a, s.M, s.K, s.lda, kBlockM);
+    if (rc) return rc;
+    rc = make_tmap(&P.tma_b, s.b, s.N, s.K, s.ldb, bn);
+    if (rc) return rc;
+    P.M = s.M; P.N = s.N; P.K = s.K;
+    P.block_n = bn;
+    P.tiles_m = (s.M + kBlockM - 1) / kBlockM;
+    P.tiles_n = 1;
+    P.tile_begin = 0;
+    P.mode = s.mode; P.act = s.act; P.drop_rate = s.drop_rate; P.layer_id = s.layer_id;
+    P.bias = s.bias;
+    P.out = static_cast<__nv_bfloat16*>(s.out); P.ldo = s.ldo;
+    P.outT = static_cast<__nv_bfloat16*>(s.outT); P.ldt = s.ldt;
+    P.outf = s.outf; P.ldf = s.ldf;
+    P.aux = static_cast<const __nv_bfloat16*>(s.aux); P.ldaux = s.ldaux;
+    P.scale = s.scale;
+    P.labels = reinterpret_cast<const long long*>(s.labels);
+    P.metrics = s.metrics;
+    P.swap = 0;
+  }
+  TTD_CUDA(cudaMemcpyAsync(device_buf, host, sizeof(GemmProblem) * count, cudaMemcpyHostToDevice,
+                           static_cast<cudaStream_t>(stream)));
+  TTD_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int ttd_gemm_chain_launch(const void* device_buf, int count, uint64_t seed, const uint64_t* step_ptr,
+                                     uint32_t flags, void* stream) {
+  if (count < 1 || count > kChainMaxStages) {
+    set_error("ttd_gemm_chain_launch: 1..%d problems, got %d", kChainMaxStages, count);
+    return -1;
+  }
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  TTD_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    TTD_CUDA(cudaFuncSetAttribute(gemm_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set[dev] = true;
+  }
+  ChainHeader h;
+  h.n = count;
+  h.seed_lo = static_cast<uint32_t>(seed);
+  h.seed_hi = static_cast<uint32_t>(seed >> 32);
+  h.step_ptr = reinterpret_cast<const unsigned long long*>(step_ptr);
+  h.use_pdl = (flags & 1u) ? 1 : 0;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(1);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kChainMaxKb * (kAStageBytes + 256 * kBlockK * 2) + 1024 + 256;
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  if (h.use_pdl) {
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  TTD_CUDA(cudaLaunchKernelEx(&cfg, gemm_chain_kernel, static_cast<const GemmProblem*>(device_buf), h));
   g_launch_count.fetch_add(1);
   return 0;
 }

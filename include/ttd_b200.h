@@ -69,6 +69,15 @@ typedef struct TtdGemmDesc {
 int ttd_gemm_group(const TtdGemmDesc* descs_host, int count, uint64_t seed, const uint64_t* step_ptr,
                    uint32_t flags, void* stream);
 
+/* Chain of small DEPENDENT problems (K <= 256, N <= 256 each) run back to back by one CTA with the same
+ * tcgen05 pipeline and epilogues: the narrow layers behind the first one cost a __syncthreads per GEMM instead
+ * of a kernel launch. Build once (synchronous; encodes tensor maps into `device_buf`, which must hold
+ * count * ttd_gemm_chain_problem_bytes() bytes, 64-byte aligned), launch every step. flags bit0: PDL. */
+uint64_t ttd_gemm_chain_problem_bytes(void);
+int ttd_gemm_chain_build(const TtdGemmDesc* descs_host, int count, void* device_buf, void* stream);
+int ttd_gemm_chain_launch(const void* device_buf, int count, uint64_t seed, const uint64_t* step_ptr,
+                          uint32_t flags, void* stream);
+
 /* ---- stand-alone softmax cross-entropy (any class count) --------------------------------- */
 /* logits fp32 [B, ldl]; labels int64 [B]; writes dlogits bf16 [B, ldd] (and transposed [C, ldt] if
  * non-NULL) = scale*(softmax - onehot)/B, and accumulates mean loss / accuracy into metrics[0..1].

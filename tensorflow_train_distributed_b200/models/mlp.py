@@ -35,6 +35,11 @@ TAIL_MAX_WIDTH = 256   # layers wider than this go through the tcgen05 GEMM, not
 TAIL_MAX_BATCH = 256
 
 
+def chain_eligible(sizes: Sequence[int], batch: int) -> bool:
+    """sizes = [n_0 .. n_L]: every layer behind the first must fit one tcgen05 tile per GEMM (K, N <= 256)."""
+    return len(sizes) >= 3 and batch <= 256 and max(sizes[1:]) <= 256 and 3 * (len(sizes) - 2) <= 32
+
+
 def tail_groups(layer_sizes: Sequence[int], batch: int, first_group: int = 0, enabled: bool = True):
     """Indices (into the layout's groups) of the dense layers the fused tail kernel takes over: every layer after
     the first one of the stack, provided all of them are narrow (their operands then live in L1/L2 and the chain
@@ -49,7 +54,7 @@ def tail_groups(layer_sizes: Sequence[int], batch: int, first_group: int = 0, en
 class GpuMlp:
     def __init__(self, store: GpuParamStore, batch: int, *, activation: str = "elu", dropout_rate: float = 0.01,
                  seed: int = 0, pdl: bool = False, keep_logits: bool = False, first_group: int = 0,
-                 feed_input: bool = True, input_grad: bool = False):
+                 feed_input: bool = True, input_grad: bool = False, chain: bool = True):
         """``first_group`` > 0 makes this the dense head of a larger model (LeNet): its input activations
         ``a[0]`` / ``aT[0]`` are then written by the stage in front (``feed_input=False``) and, with
         ``input_grad``, the backward pass also produces ``dz0`` = dL/d(input) * act'(input) for that stage."""
@@ -82,9 +87,16 @@ class GpuMlp:
         self.x_pool: Optional[torch.Tensor] = None
         self.labels_pool: Optional[torch.Tensor] = None
         self.use_tail = all((first_group + l) in store.tail_groups for l in range(1, self.L)) and self.L >= 2
+        # chain: the narrow layers behind the first run as ONE single-CTA tcgen05 kernel (gemm_chain_kernel)
+        self.use_chain = (not self.use_tail) and chain and chain_eligible(sizes, batch)
         self._build_descs()
         if self.use_tail:
             self._build_tail()
+        if self.use_chain:
+            stages = list(self.fwd_descs[1:])
+            stages += [grp[1] for grp in self.bwd_descs[:-1]]   # dgrad of layers L..2: the critical path
+            stages += [grp[0] for grp in self.bwd_descs[:-1]]   # then their weight gradients
+            self._chain = gemm.GemmChain(stages, dev)
 
     def set_device_dataset(self, x_pool: Optional[torch.Tensor], labels_pool: Optional[torch.Tensor]) -> None:
         """Train from a device-resident pool [P, B, F] / [P, B]: batch ``local_step % P`` is picked on the
@@ -194,6 +206,10 @@ class GpuMlp:
         if self.use_tail:  # first layer on the tensor cores, everything behind it in one fused launch
             gemm.gemm_group([self.fwd_descs[0]], seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
             return 1 + self.launch_tail()
+        if self.use_chain:  # layers 2..L forward + loss + their whole backward: one single-CTA launch
+            gemm.gemm_group([self.fwd_descs[0]], seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
+            self._chain.launch(seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
+            return 2
         for d in self.fwd_descs:
             gemm.gemm_group([d], seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
             n += 1
@@ -201,7 +217,7 @@ class GpuMlp:
 
     def launch_backward(self) -> int:
         step_ptr, n = self.store.local_step_ptr, 0
-        if self.use_tail:  # the tail already produced dz of the first layer and every other gradient
+        if self.use_tail or self.use_chain:  # dz of the first layer and every other gradient exist already
             gemm.gemm_group(self.bwd_descs[-1], seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
             return 1
         for grp in self.bwd_descs:

@@ -112,3 +112,21 @@ def prep_input(x: torch.Tensor, xb: Optional[torch.Tensor], xT: Optional[torch.T
                                N.ptr(xT), _ld(xT) if xT is not None else 0, N.ptr(labels_pool), N.ptr(labels_out),
                                pool, step_ptr, N.ptr(xf), 1 if pdl else 0, N.cur_stream())
     N.check(rc, "ttd_prep_input")
+
+
+class GemmChain:
+    """A fixed list of small dependent GEMM problems executed by ONE CTA per launch (``gemm_chain_kernel``)."""
+
+    def __init__(self, descs: Sequence[N.GemmDesc], device: torch.device):
+        lib = N.load()
+        self.n = len(descs)
+        nbytes = int(lib.ttd_gemm_chain_problem_bytes()) * self.n
+        self.buf = torch.zeros(nbytes + 64, dtype=torch.uint8, device=device)
+        self.ptr = (self.buf.data_ptr() + 63) & ~63
+        arr = (N.GemmDesc * self.n)(*descs)
+        N.check(lib.ttd_gemm_chain_build(arr, self.n, self.ptr, N.cur_stream()), "ttd_gemm_chain_build")
+
+    def launch(self, *, seed: int = 0, step_ptr: Optional[int] = None, pdl: bool = False) -> None:
+        lib = N.load()
+        N.check(lib.ttd_gemm_chain_launch(self.ptr, self.n, C.c_uint64(seed & (2**64 - 1)), step_ptr,
+                                          1 if pdl else 0, N.cur_stream()), "ttd_gemm_chain_launch")

@@ -59,10 +59,11 @@ class GpuTrainer:
         self.hyper = hyper_from_config(cfg, n_agg)
         with torch.cuda.stream(self.stream):
             lenet = cfg.model == "lenet"
+            cluster_tail = cfg.fused_tail and cfg.tail_impl == "cluster"
             if lenet:  # dense head = groups 2.. (fc1, fc2, output); its first layer stays on the GEMM path
-                tail = mlp_model.tail_groups([120, 84, cfg.num_classes], cfg.batch_size, 2, cfg.fused_tail)
+                tail = mlp_model.tail_groups([120, 84, cfg.num_classes], cfg.batch_size, 2, cluster_tail)
             else:
-                tail = mlp_model.tail_groups(cfg.layer_sizes, cfg.batch_size, 0, cfg.fused_tail)
+                tail = mlp_model.tail_groups(cfg.layer_sizes, cfg.batch_size, 0, cluster_tail)
             self.store = GpuParamStore(self.layout, self.hyper, self.device, comm=comm, need_w_rm_first=lenet,
                                        pull_fused_first=self.sync and self.world > 1 and cfg.pull_fused and not lenet,
                                        tail_groups=tail)
@@ -89,10 +90,12 @@ class GpuTrainer:
         cfg = self.cfg
         if cfg.model in ("mlp", "wide_mlp"):
             return mlp_model.GpuMlp(self.store, cfg.batch_size, activation=cfg.activation,
-                                    dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank, pdl=cfg.pdl)
+                                    dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank, pdl=cfg.pdl,
+                                    chain=cfg.fused_tail and cfg.tail_impl == "chain")
         from ..models import lenet
         return lenet.GpuLeNet(self.store, cfg.batch_size, activation=cfg.activation,
-                              dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank, pdl=cfg.pdl)
+                              dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank, pdl=cfg.pdl,
+                              chain=cfg.fused_tail and cfg.tail_impl == "chain")
 
     # -------------------------------------------------------------------------------------------
     def initialize(self, restore: Optional[Dict[str, np.ndarray]] = None) -> None:

@@ -30,12 +30,14 @@ def _torch_reference(vars_, x, y, sizes, act="elu"):
     return loss.item(), (h.argmax(1) == y).float().mean().item(), ws, bs
 
 
-@pytest.mark.parametrize("act,fused_tail", [("elu", True), ("relu", True), ("elu", False), ("relu", False)])
-def test_step_gradients_match_autograd(act, fused_tail):
-    """Both back ends of the narrow layers: the fused cluster kernel and one tcgen05 GEMM per layer."""
+@pytest.mark.parametrize("act,tail", [("elu", "chain"), ("relu", "chain"), ("elu", "cluster"), ("relu", "none")])
+def test_step_gradients_match_autograd(act, tail):
+    """All back ends of the narrow layers: the single-CTA tcgen05 chain kernel, the fp32 cluster kernel and one
+    tcgen05 GEMM launch per layer."""
     from tensorflow_train_distributed_b200.data import synthetic_mnist
     from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
-    cfg = _cfg(dropout_rate=0.0, cuda_graph=False, activation=act, fused_tail=fused_tail)
+    cfg = _cfg(dropout_rate=0.0, cuda_graph=False, activation=act, fused_tail=tail != "none",
+               tail_impl=tail if tail != "none" else "chain")
     tr = GpuTrainer(cfg)
     tr.initialize()
     ds = synthetic_mnist(1024, seed=5)
@@ -207,7 +209,7 @@ def test_fused_tail_follows_the_per_layer_path_with_dropout():
     from tensorflow_train_distributed_b200.data import synthetic_mnist
     from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
     ds1, ds2 = synthetic_mnist(4096, seed=6), synthetic_mnist(4096, seed=6)
-    a = GpuTrainer(_cfg(dropout_rate=0.2, fused_tail=True))
+    a = GpuTrainer(_cfg(dropout_rate=0.2, fused_tail=True, tail_impl="cluster"))
     b = GpuTrainer(_cfg(dropout_rate=0.2, fused_tail=False))
     a.initialize(), b.initialize()
     for i in range(40):
@@ -222,4 +224,25 @@ def test_fused_tail_follows_the_per_layer_path_with_dropout():
     for k in ("hidden1/kernel", "hidden3/kernel", "output/bias"):
         cos = float(np.dot(wa[k].ravel(), wb[k].ravel()) / (np.linalg.norm(wa[k]) * np.linalg.norm(wb[k]) + 1e-12))
         assert cos > 0.999, (k, cos)
+    a.close(), b.close()
+
+
+def test_chain_kernel_is_bitwise_the_per_layer_path():
+    """The chain kernel runs the very same tcgen05 pipeline and epilogues as one launch per layer would: with
+    identical seeds the two trainers must stay together to the last bit of the loss (atomics aside)."""
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    ds1, ds2 = synthetic_mnist(4096, seed=6), synthetic_mnist(4096, seed=6)
+    a = GpuTrainer(_cfg(dropout_rate=0.1, fused_tail=True, tail_impl="chain"))
+    b = GpuTrainer(_cfg(dropout_rate=0.1, fused_tail=False))
+    a.initialize(), b.initialize()
+    assert a.launches_per_step == 5 and b.launches_per_step == 12
+    for _ in range(30):
+        xa, ya = ds1.next_batch(128)
+        xb, yb = ds2.next_batch(128)
+        va, vb = a.train_step(xa, ya), b.train_step(xb, yb)
+    assert abs(va.loss - vb.loss) < 1e-5 and va.global_step == vb.global_step == 30
+    wa, wb = a.export_variables(), b.export_variables()
+    for k in wa:
+        assert np.allclose(wa[k], wb[k], atol=1e-6), k
     a.close(), b.close()
