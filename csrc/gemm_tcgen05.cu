@@ -753,9 +753,21 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_chain_kernel(const GemmProbl
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   }
   const EpiCtx E{h.seed_lo, h.seed_hi, h.step_ptr, smem};
+  // The descriptor of the stage in flight is staged in shared memory: the epilogue consults it inside its
+  // innermost loops, and global-memory loads there (which the compiler cannot hoist past the stores) would
+  // cost more than the GEMM. Only the tensor maps are used in place (TMA wants them in global memory).
+  __shared__ __align__(64) GemmProblem sP;
   uint32_t ph = 0;
   for (int s = 0; s < h.n; ++s) {
-    const GemmProblem& P = probs[s];
+    {
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(&probs[s]);
+      uint32_t* dst = reinterpret_cast<uint32_t*>(&sP);
+      for (int i = threadIdx.x; i < static_cast<int>(sizeof(GemmProblem) / 4); i += kThreads) dst[i] = src[i];
+    }
+    __syncthreads();
+    const GemmProblem& P = sP;
+    const CUtensorMap* map_a = &probs[s].tma_a;
+    const CUtensorMap* map_b = &probs[s].tma_b;
     const int num_kb = (P.K + kBlockK - 1) / kBlockK;
     const int b_kb_bytes = P.block_n * kBlockK * 2;
     for (int tile = 0; tile < P.tiles_m * P.tiles_n; ++tile) {
@@ -763,8 +775,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_chain_kernel(const GemmProbl
       if (warp == 0 && lane == 0) {
         mbar_arrive_expect_tx(full_bar, static_cast<uint32_t>(num_kb * (kAStageBytes + b_kb_bytes)));
         for (int kb = 0; kb < num_kb; ++kb) {
-          tma_load_2d(sA + kb * kAStageBytes, &P.tma_a, full_bar, kb * kBlockK, m0);
-          tma_load_2d(sB + kb * b_kb_bytes, &P.tma_b, full_bar, kb * kBlockK, nbase);
+          tma_load_2d(sA + kb * kAStageBytes, map_a, full_bar, kb * kBlockK, m0);
+          tma_load_2d(sB + kb * b_kb_bytes, map_b, full_bar, kb * kBlockK, nbase);
         }
       } else if (warp == 1 && lane == 0) {
         const uint32_t idesc = umma_idesc_bf16(kBlockM, static_cast<uint32_t>(P.block_n));
