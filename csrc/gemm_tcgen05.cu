@@ -878,7 +878,8 @@ extern "C" int ttd_gemm_chain_launch(const void* device_buf, int count, uint64_t
   int dev = 0;
   TTD_CUDA(cudaGetDevice(&dev));
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    TTD_CUDA(cudaFuncSetAttribute(gemm_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    TTD_CUDA(cudaFuncSetAttribute(gemm_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  kChainMaxKb * (kAStageBytes + 256 * kBlockK * 2) + 1024 + 256));
     attr_set[dev] = true;
   }
   ChainHeader h;
