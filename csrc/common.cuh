@@ -226,6 +226,22 @@ __device__ __forceinline__ Philox4 dropout_block(uint32_t row, uint32_t col4, ui
   return philox4x32_10(row, col4, static_cast<uint32_t>(step), (static_cast<uint32_t>(step >> 32) << 8) ^ layer,
                        seed_lo, seed_hi);
 }
+// Dropout draws 16 random bits per element: one Philox block serves EIGHT consecutive columns of a row
+// (block = (row, col >> 3), lane = col & 7), which halves the RNG work of the epilogues; the keep decision is
+// lane16 >= rate * 65536 (granularity 1.5e-5, far below any rate in use).
+__device__ __forceinline__ uint32_t dropout_thresh16(float rate) {
+  const float t = fminf(fmaxf(rate, 0.0f), 1.0f) * 65536.0f;
+  return t >= 65535.0f ? 65535u : static_cast<uint32_t>(t);
+}
+__device__ __forceinline__ uint32_t dropout_lane16(const Philox4& p, int lane) {
+  const uint32_t w = (lane >> 1) == 0 ? p.x : ((lane >> 1) == 1 ? p.y : ((lane >> 1) == 2 ? p.z : p.w));
+  return (lane & 1) ? (w >> 16) : (w & 0xFFFFu);
+}
+__device__ __forceinline__ bool dropout_kept(uint32_t row, uint32_t col, uint64_t step, uint32_t layer, uint32_t s0,
+                                             uint32_t s1, uint32_t thresh16) {
+  const Philox4 p = dropout_block(row, col >> 3, step, layer, s0, s1);
+  return dropout_lane16(p, static_cast<int>(col & 7u)) >= thresh16;
+}
 __device__ __forceinline__ uint32_t philox_pick(const Philox4& p, int i) {
   return i == 0 ? p.x : (i == 1 ? p.y : (i == 2 ? p.z : p.w));
 }

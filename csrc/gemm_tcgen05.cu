@@ -106,6 +106,74 @@ __device__ __forceinline__ void store_row_chunk(const GemmProblem& P, int m, int
   }
 }
 
+// One row x 16 columns of a forward / dgrad epilogue with mode, activation and dropout fixed at compile time.
+// `full`: all 16 columns exist (vector loads of bias / saved activation, no per-element bounds tests).
+template <int MODE, int ACT, bool DROP>
+__device__ __forceinline__ void epi_fd_chunk(const GemmProblem& P, const EpiCtx& E, int m, int n0, float* v,
+                                             unsigned long long step, float keep, float inv_keep, uint32_t thresh16,
+                                             bool full) {
+  float side[16];  // FWD: bias; DGRAD: saved (post-dropout) activation of the layer being differentiated
+  if (MODE == TTD_EPI_FWD) {
+    if (P.bias == nullptr) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) side[j] = 0.0f;
+    } else if (full && (reinterpret_cast<uintptr_t>(P.bias + n0) & 15u) == 0) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4 t = *reinterpret_cast<const float4*>(P.bias + n0 + 4 * q);
+        side[4 * q] = t.x; side[4 * q + 1] = t.y; side[4 * q + 2] = t.z; side[4 * q + 3] = t.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) side[j] = (n0 + j < P.N) ? P.bias[n0 + j] : 0.0f;
+    }
+  } else {
+    if (P.aux == nullptr) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) side[j] = 1.0f;
+    } else {
+      const __nv_bfloat16* arow = P.aux + static_cast<long long>(m) * P.ldaux + n0;
+      if (full && (reinterpret_cast<uintptr_t>(arow) & 15u) == 0) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const uint4 u = *reinterpret_cast<const uint4*>(arow + 8 * h);
+          const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const __nv_bfloat162 t = *reinterpret_cast<const __nv_bfloat162*>(&w[q]);
+            side[8 * h + 2 * q] = __low2float(t);
+            side[8 * h + 2 * q + 1] = __high2float(t);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) side[j] = (n0 + j < P.N) ? __bfloat162float(arow[j]) : 0.0f;
+      }
+    }
+  }
+  Philox4 rnd[2];
+  if (DROP) {
+    rnd[0] = dropout_block(static_cast<uint32_t>(m), static_cast<uint32_t>(n0 >> 3), step, P.layer_id, E.seed_lo, E.seed_hi);
+    rnd[1] = dropout_block(static_cast<uint32_t>(m), static_cast<uint32_t>((n0 >> 3) + 1), step, P.layer_id, E.seed_lo,
+                           E.seed_hi);
+  }
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const bool kept = !DROP || dropout_lane16(rnd[j >> 3], j & 7) >= thresh16;
+    float r;
+    if (MODE == TTD_EPI_FWD) {
+      const float a = act_apply(v[j] + side[j], ACT);
+      if (P.outf != nullptr && (full || n0 + j < P.N)) P.outf[static_cast<long long>(m) * P.ldf + n0 + j] = a;
+      r = DROP ? (kept ? a * inv_keep : 0.0f) : a;
+    } else {
+      const float g = v[j] * act_grad_from_out(DROP ? side[j] * keep : side[j], ACT);
+      r = DROP ? (kept ? g * inv_keep : 0.0f) : g;
+    }
+    v[j] = (full || n0 + j < P.N) ? r : 0.0f;
+  }
+  store_row_chunk(P, m, n0, v);
+}
+
 // Everything the four epilogue warps do with a finished accumulator tile (rows m0.., columns nbase.. of problem P):
 // shared by the one-tile-per-CTA kernel and by the chain kernel, which walks a list of dependent problems.
 struct EpiCtx {
@@ -189,7 +257,7 @@ __device__ __forceinline__ void run_epilogue(const GemmProblem& P, const EpiCtx&
     const float inv_keep = 1.0f / keep;
     const bool wide_store = P.mode == TTD_EPI_WGRAD && (P.block_n % 32) == 0 && (P.N % 4) == 0 && (P.ldf % 4) == 0 &&
                             (reinterpret_cast<uintptr_t>(P.outf) & 15u) == 0;
-    const uint32_t drop_thresh = static_cast<uint32_t>(fminf(P.drop_rate, 1.0f) * 4294967040.0f);
+    const uint32_t drop_thresh = dropout_thresh16(P.drop_rate);
     for (int c = 0; c < nchunks; ++c) {
       const int n0 = nbase + c * 16;
       __syncwarp();                      // tcgen05.ld is warp-collective: reconverge before it
@@ -246,9 +314,8 @@ __device__ __forceinline__ void run_epilogue(const GemmProblem& P, const EpiCtx&
           if (b < P.N) {
             bool kept = true;
             if (P.drop_rate > 0.0f) {
-              const Philox4 rnd = dropout_block(static_cast<uint32_t>(b), static_cast<uint32_t>(f >> 2), step,
-                                                P.layer_id, E.seed_lo, E.seed_hi);
-              kept = philox_pick(rnd, f & 3) >= drop_thresh;
+              kept = dropout_kept(static_cast<uint32_t>(b), static_cast<uint32_t>(f), step, P.layer_id, E.seed_lo,
+                                  E.seed_hi, drop_thresh);
             }
             if (P.mode == TTD_EPI_FWD) {
               const float a = act_apply(v[j] + bias_f, P.act);
@@ -281,42 +348,23 @@ __device__ __forceinline__ void run_epilogue(const GemmProblem& P, const EpiCtx&
           }
         }
       } else if (live) {
-        float a_saved[16];
-        if (P.mode == TTD_EPI_DGRAD && P.aux != nullptr) {
-          const __nv_bfloat16* arow = P.aux + static_cast<long long>(m) * P.ldaux;
-#pragma unroll
-          for (int j = 0; j < 16; ++j) a_saved[j] = (n0 + j < P.N) ? __bfloat162float(arow[n0 + j]) : 0.0f;
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) a_saved[j] = 1.0f;
+        // straight-line code per (mode, activation, dropout): no per-element mode tests in the hot loop
+        const bool full = n0 + 16 <= P.N;
+        const int key = (P.mode == TTD_EPI_DGRAD ? 6 : 0) + P.act * 2 + (P.drop_rate > 0.0f ? 1 : 0);
+        switch (key) {
+          case 0: epi_fd_chunk<TTD_EPI_FWD, ACT_NONE, false>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
+          case 1: epi_fd_chunk<TTD_EPI_FWD, ACT_NONE, true>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
+          case 2: epi_fd_chunk<TTD_EPI_FWD, ACT_RELU, false>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
+          case 3: epi_fd_chunk<TTD_EPI_FWD, ACT_RELU, true>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
+          case 4: epi_fd_chunk<TTD_EPI_FWD, ACT_ELU, false>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
+          case 5: epi_fd_chunk<TTD_EPI_FWD, ACT_ELU, true>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
+          case 6: epi_fd_chunk<TTD_EPI_DGRAD, ACT_NONE, false>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
+          case 7: epi_fd_chunk<TTD_EPI_DGRAD, ACT_NONE, true>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
+          case 8: epi_fd_chunk<TTD_EPI_DGRAD, ACT_RELU, false>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
+          case 9: epi_fd_chunk<TTD_EPI_DGRAD, ACT_RELU, true>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
+          case 10: epi_fd_chunk<TTD_EPI_DGRAD, ACT_ELU, false>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
+          default: epi_fd_chunk<TTD_EPI_DGRAD, ACT_ELU, true>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
         }
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          Philox4 rnd{0, 0, 0, 0};
-          if (P.drop_rate > 0.0f)
-            rnd = dropout_block(static_cast<uint32_t>(m), static_cast<uint32_t>((n0 >> 2) + q), step, P.layer_id,
-                                E.seed_lo, E.seed_hi);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int j = 4 * q + i;
-            const int n = n0 + j;
-            float r = 0.0f;
-            if (n < P.N) {
-              const bool kept = (P.drop_rate <= 0.0f) || (philox_pick(rnd, i) >= drop_thresh);
-              if (P.mode == TTD_EPI_FWD) {
-                const float z = v[j] + (P.bias ? P.bias[n] : 0.0f);
-                const float a = act_apply(z, P.act);
-                if (P.outf) P.outf[static_cast<long long>(m) * P.ldf + n] = a;
-                r = kept ? a * inv_keep : 0.0f;
-              } else {  // DGRAD
-                const float a = a_saved[j] * keep;  // undo the 1/keep scaling of the saved activation
-                r = kept ? v[j] * inv_keep * act_grad_from_out(a, P.act) : 0.0f;
-              }
-            }
-            v[j] = r;
-          }
-        }
-        store_row_chunk(P, m, n0, v);
       }
     }
   }

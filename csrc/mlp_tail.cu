@@ -93,8 +93,7 @@ __device__ __forceinline__ void tail_gemm(int R, int C, int K4, const XT* __rest
 __device__ __forceinline__ bool tail_kept(float rate, uint32_t thresh, int r, int c, unsigned long long step,
                                           uint32_t layer_id, uint32_t s0, uint32_t s1) {
   if (rate <= 0.0f) return true;
-  const Philox4 p = dropout_block(static_cast<uint32_t>(r), static_cast<uint32_t>(c >> 2), step, layer_id, s0, s1);
-  return philox_pick(p, c & 3) >= thresh;
+  return dropout_kept(static_cast<uint32_t>(r), static_cast<uint32_t>(c), step, layer_id, s0, s1, thresh);
 }
 
 __global__ void __launch_bounds__(kTailThreads, 1) mlp_tail_kernel(const __grid_constant__ TailParams P) {
@@ -117,7 +116,7 @@ __global__ void __launch_bounds__(kTailThreads, 1) mlp_tail_kernel(const __grid_
     const TtdTailLayer& Ly = d.layer[l];
     const bool last = l == L - 1;
     const float keep = 1.0f - Ly.drop_rate, inv_keep = 1.0f / keep;
-    const uint32_t thresh = static_cast<uint32_t>(fminf(Ly.drop_rate, 1.0f) * 4294967040.0f);
+    const uint32_t thresh = dropout_thresh16(Ly.drop_rate);
     float* out = Ly.act;            // [B][ld_act]: post-dropout activation, or the logits for the last layer
     float* outT = Ly.actT;          // [out+1][ld_actT] (hidden layers only)
     auto epi = [&](int r, int c, float v) {
@@ -182,7 +181,7 @@ __global__ void __launch_bounds__(kTailThreads, 1) mlp_tail_kernel(const __grid_
     if (l > 0) {
       const TtdTailLayer& Lp = d.layer[l - 1];  // the layer whose pre-activation gradient we produce
       const float keep = 1.0f - Lp.drop_rate, inv_keep = 1.0f / keep;
-      const uint32_t thresh = static_cast<uint32_t>(fminf(Lp.drop_rate, 1.0f) * 4294967040.0f);
+      const uint32_t thresh = dropout_thresh16(Lp.drop_rate);
       auto epi = [&](int r, int c, float v) {
         const float a_sv = Lp.act[static_cast<long long>(r) * Lp.ld_act + c];
         const bool kept = tail_kept(Lp.drop_rate, thresh, r, c, step, Lp.layer_id, s0, s1);
@@ -193,7 +192,7 @@ __global__ void __launch_bounds__(kTailThreads, 1) mlp_tail_kernel(const __grid_
     } else {
       // gradient for the layer in front of the tail (the tcgen05 first layer): bf16, both layouts
       const float keep = 1.0f - d.in_drop_rate, inv_keep = 1.0f / keep;
-      const uint32_t thresh = static_cast<uint32_t>(fminf(d.in_drop_rate, 1.0f) * 4294967040.0f);
+      const uint32_t thresh = dropout_thresh16(d.in_drop_rate);
       const __nv_bfloat16* a_in = static_cast<const __nv_bfloat16*>(d.a_in);
       __nv_bfloat16* dzi = static_cast<__nv_bfloat16*>(d.dz_in);
       __nv_bfloat16* dziT = static_cast<__nv_bfloat16*>(d.dz_inT);
