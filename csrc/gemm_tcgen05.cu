@@ -106,6 +106,14 @@ __device__ __forceinline__ void store_row_chunk(const GemmProblem& P, int m, int
   }
 }
 
+// Everything the four epilogue warps do with a finished accumulator tile (rows m0.., columns nbase.. of problem P):
+// shared by the one-tile-per-CTA kernel and by the chain kernel, which walks a list of dependent problems.
+struct EpiCtx {
+  uint32_t seed_lo, seed_hi;
+  const unsigned long long* step_ptr;
+  uint8_t* smem;  // idle pipeline stages, reused as a staging patch by the wgrad epilogue
+};
+
 // One row x 16 columns of a forward / dgrad epilogue with mode, activation and dropout fixed at compile time.
 // `full`: all 16 columns exist (vector loads of bias / saved activation, no per-element bounds tests).
 template <int MODE, int ACT, bool DROP>
@@ -173,14 +181,6 @@ __device__ __forceinline__ void epi_fd_chunk(const GemmProblem& P, const EpiCtx&
   }
   store_row_chunk(P, m, n0, v);
 }
-
-// Everything the four epilogue warps do with a finished accumulator tile (rows m0.., columns nbase.. of problem P):
-// shared by the one-tile-per-CTA kernel and by the chain kernel, which walks a list of dependent problems.
-struct EpiCtx {
-  uint32_t seed_lo, seed_hi;
-  const unsigned long long* step_ptr;
-  uint8_t* smem;  // idle pipeline stages, reused as a staging patch by the wgrad epilogue
-};
 
 __device__ __forceinline__ void run_epilogue(const GemmProblem& P, const EpiCtx& E, uint32_t tmem_base, int m0,
                                              int nbase, int warp, int lane) {
