@@ -114,31 +114,36 @@ struct EpiCtx {
   uint8_t* smem;  // idle pipeline stages, reused as a staging patch by the wgrad epilogue
 };
 
-// One row x 16 columns of a forward / dgrad epilogue with mode, activation and dropout fixed at compile time.
-// `full`: all 16 columns exist (vector loads of bias / saved activation, no per-element bounds tests).
-template <int MODE, int ACT, bool DROP>
-__device__ __forceinline__ void epi_fd_chunk(const GemmProblem& P, const EpiCtx& E, int m, int n0, float* v,
-                                             unsigned long long step, float keep, float inv_keep, uint32_t thresh16,
-                                             bool full) {
-  float side[16];  // FWD: bias; DGRAD: saved (post-dropout) activation of the layer being differentiated
-  if (MODE == TTD_EPI_FWD) {
+// What a forward / dgrad chunk (one row x 16 columns) needs besides the accumulator: bias or saved activation,
+// and the dropout bits. None of it depends on the GEMM, so it is fetched while TMA and the tensor core are
+// still busy (chunk 0) or while the previous chunk is being finished (later chunks).
+struct EpiSide {
+  float side[16];   // FWD: bias; DGRAD: saved (post-dropout) activation of the layer being differentiated
+  Philox4 rnd[2];   // 16 random bits per column, eight columns per block
+};
+
+__device__ __forceinline__ void epi_fd_load(const GemmProblem& P, const EpiCtx& E, int m, int n0,
+                                            unsigned long long step, bool row_ok, EpiSide& S) {
+  if (!row_ok || n0 >= P.N) return;
+  const bool full = n0 + 16 <= P.N;
+  if (P.mode == TTD_EPI_FWD) {
     if (P.bias == nullptr) {
 #pragma unroll
-      for (int j = 0; j < 16; ++j) side[j] = 0.0f;
+      for (int j = 0; j < 16; ++j) S.side[j] = 0.0f;
     } else if (full && (reinterpret_cast<uintptr_t>(P.bias + n0) & 15u) == 0) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const float4 t = *reinterpret_cast<const float4*>(P.bias + n0 + 4 * q);
-        side[4 * q] = t.x; side[4 * q + 1] = t.y; side[4 * q + 2] = t.z; side[4 * q + 3] = t.w;
+        S.side[4 * q] = t.x; S.side[4 * q + 1] = t.y; S.side[4 * q + 2] = t.z; S.side[4 * q + 3] = t.w;
       }
     } else {
 #pragma unroll
-      for (int j = 0; j < 16; ++j) side[j] = (n0 + j < P.N) ? P.bias[n0 + j] : 0.0f;
+      for (int j = 0; j < 16; ++j) S.side[j] = (n0 + j < P.N) ? P.bias[n0 + j] : 0.0f;
     }
   } else {
     if (P.aux == nullptr) {
 #pragma unroll
-      for (int j = 0; j < 16; ++j) side[j] = 1.0f;
+      for (int j = 0; j < 16; ++j) S.side[j] = 1.0f;
     } else {
       const __nv_bfloat16* arow = P.aux + static_cast<long long>(m) * P.ldaux + n0;
       if (full && (reinterpret_cast<uintptr_t>(arow) & 15u) == 0) {
@@ -149,32 +154,39 @@ __device__ __forceinline__ void epi_fd_chunk(const GemmProblem& P, const EpiCtx&
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             const __nv_bfloat162 t = *reinterpret_cast<const __nv_bfloat162*>(&w[q]);
-            side[8 * h + 2 * q] = __low2float(t);
-            side[8 * h + 2 * q + 1] = __high2float(t);
+            S.side[8 * h + 2 * q] = __low2float(t);
+            S.side[8 * h + 2 * q + 1] = __high2float(t);
           }
         }
       } else {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) side[j] = (n0 + j < P.N) ? __bfloat162float(arow[j]) : 0.0f;
+        for (int j = 0; j < 16; ++j) S.side[j] = (n0 + j < P.N) ? __bfloat162float(arow[j]) : 0.0f;
       }
     }
   }
-  Philox4 rnd[2];
-  if (DROP) {
-    rnd[0] = dropout_block(static_cast<uint32_t>(m), static_cast<uint32_t>(n0 >> 3), step, P.layer_id, E.seed_lo, E.seed_hi);
-    rnd[1] = dropout_block(static_cast<uint32_t>(m), static_cast<uint32_t>((n0 >> 3) + 1), step, P.layer_id, E.seed_lo,
-                           E.seed_hi);
+  if (P.drop_rate > 0.0f) {
+    S.rnd[0] = dropout_block(static_cast<uint32_t>(m), static_cast<uint32_t>(n0 >> 3), step, P.layer_id, E.seed_lo,
+                             E.seed_hi);
+    S.rnd[1] = dropout_block(static_cast<uint32_t>(m), static_cast<uint32_t>((n0 >> 3) + 1), step, P.layer_id,
+                             E.seed_lo, E.seed_hi);
   }
+}
+
+// The arithmetic of one chunk with mode, activation and dropout fixed at compile time (straight-line code).
+template <int MODE, int ACT, bool DROP>
+__device__ __forceinline__ void epi_fd_apply(const GemmProblem& P, int m, int n0, float* v, const EpiSide& S,
+                                             float keep, float inv_keep, uint32_t thresh16) {
+  const bool full = n0 + 16 <= P.N;
 #pragma unroll
   for (int j = 0; j < 16; ++j) {
-    const bool kept = !DROP || dropout_lane16(rnd[j >> 3], j & 7) >= thresh16;
+    const bool kept = !DROP || dropout_lane16(S.rnd[j >> 3], j & 7) >= thresh16;
     float r;
     if (MODE == TTD_EPI_FWD) {
-      const float a = act_apply(v[j] + side[j], ACT);
+      const float a = act_apply(v[j] + S.side[j], ACT);
       if (P.outf != nullptr && (full || n0 + j < P.N)) P.outf[static_cast<long long>(m) * P.ldf + n0 + j] = a;
       r = DROP ? (kept ? a * inv_keep : 0.0f) : a;
     } else {
-      const float g = v[j] * act_grad_from_out(DROP ? side[j] * keep : side[j], ACT);
+      const float g = v[j] * act_grad_from_out(DROP ? S.side[j] * keep : S.side[j], ACT);
       r = DROP ? (kept ? g * inv_keep : 0.0f) : g;
     }
     v[j] = (full || n0 + j < P.N) ? r : 0.0f;
@@ -183,7 +195,7 @@ __device__ __forceinline__ void epi_fd_chunk(const GemmProblem& P, const EpiCtx&
 }
 
 __device__ __forceinline__ void run_epilogue(const GemmProblem& P, const EpiCtx& E, uint32_t tmem_base, int m0,
-                                             int nbase, int warp, int lane) {
+                                             int nbase, int warp, int lane, uint64_t* acc_bar, uint32_t acc_parity) {
   // ===================== epilogue: TMEM -> registers -> global =====================
   const int quad = warp & 3;  // TMEM lane quadrant this warp may read
   const int m = m0 + quad * 32 + lane;
@@ -192,6 +204,12 @@ __device__ __forceinline__ void run_epilogue(const GemmProblem& P, const EpiCtx&
   const uint32_t taddr_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
   const int nchunks = P.block_n / 16;
   float v[16];
+  // everything that does not need the accumulator happens BEFORE the wait on it
+  const bool fd = (P.mode == TTD_EPI_FWD || P.mode == TTD_EPI_DGRAD) && !P.swap;
+  EpiSide S0, S1;
+  if (fd) epi_fd_load(P, E, m, nbase, step, row_ok, S0);
+  mbar_wait(acc_bar, acc_parity);
+  tc_fence_after();
 
   if (P.mode == TTD_EPI_FWD_XENT) {
     // One thread owns one example's whole logit row (N <= block_n). Three cheap passes over TMEM.
@@ -348,23 +366,25 @@ __device__ __forceinline__ void run_epilogue(const GemmProblem& P, const EpiCtx&
           }
         }
       } else if (live) {
-        // straight-line code per (mode, activation, dropout): no per-element mode tests in the hot loop
-        const bool full = n0 + 16 <= P.N;
+        // straight-line code per (mode, activation, dropout); the next chunk's side data is requested first so
+        // that its latency hides behind this chunk's arithmetic and stores
+        if (c + 1 < nchunks) epi_fd_load(P, E, m, n0 + 16, step, row_ok, S1);
         const int key = (P.mode == TTD_EPI_DGRAD ? 6 : 0) + P.act * 2 + (P.drop_rate > 0.0f ? 1 : 0);
         switch (key) {
-          case 0: epi_fd_chunk<TTD_EPI_FWD, ACT_NONE, false>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
-          case 1: epi_fd_chunk<TTD_EPI_FWD, ACT_NONE, true>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
-          case 2: epi_fd_chunk<TTD_EPI_FWD, ACT_RELU, false>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
-          case 3: epi_fd_chunk<TTD_EPI_FWD, ACT_RELU, true>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
-          case 4: epi_fd_chunk<TTD_EPI_FWD, ACT_ELU, false>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
-          case 5: epi_fd_chunk<TTD_EPI_FWD, ACT_ELU, true>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
-          case 6: epi_fd_chunk<TTD_EPI_DGRAD, ACT_NONE, false>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
-          case 7: epi_fd_chunk<TTD_EPI_DGRAD, ACT_NONE, true>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
-          case 8: epi_fd_chunk<TTD_EPI_DGRAD, ACT_RELU, false>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
-          case 9: epi_fd_chunk<TTD_EPI_DGRAD, ACT_RELU, true>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
-          case 10: epi_fd_chunk<TTD_EPI_DGRAD, ACT_ELU, false>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
-          default: epi_fd_chunk<TTD_EPI_DGRAD, ACT_ELU, true>(P, E, m, n0, v, step, keep, inv_keep, drop_thresh, full); break;
+          case 0: epi_fd_apply<TTD_EPI_FWD, ACT_NONE, false>(P, m, n0, v, S0, keep, inv_keep, drop_thresh); break;
+          case 1: epi_fd_apply<TTD_EPI_FWD, ACT_NONE, true>(P, m, n0, v, S0, keep, inv_keep, drop_thresh); break;
+          case 2: epi_fd_apply<TTD_EPI_FWD, ACT_RELU, false>(P, m, n0, v, S0, keep, inv_keep, drop_thresh); break;
+          case 3: epi_fd_apply<TTD_EPI_FWD, ACT_RELU, true>(P, m, n0, v, S0, keep, inv_keep, drop_thresh); break;
+          case 4: epi_fd_apply<TTD_EPI_FWD, ACT_ELU, false>(P, m, n0, v, S0, keep, inv_keep, drop_thresh); break;
+          case 5: epi_fd_apply<TTD_EPI_FWD, ACT_ELU, true>(P, m, n0, v, S0, keep, inv_keep, drop_thresh); break;
+          case 6: epi_fd_apply<TTD_EPI_DGRAD, ACT_NONE, false>(P, m, n0, v, S0, keep, inv_keep, drop_thresh); break;
+          case 7: epi_fd_apply<TTD_EPI_DGRAD, ACT_NONE, true>(P, m, n0, v, S0, keep, inv_keep, drop_thresh); break;
+          case 8: epi_fd_apply<TTD_EPI_DGRAD, ACT_RELU, false>(P, m, n0, v, S0, keep, inv_keep, drop_thresh); break;
+          case 9: epi_fd_apply<TTD_EPI_DGRAD, ACT_RELU, true>(P, m, n0, v, S0, keep, inv_keep, drop_thresh); break;
+          case 10: epi_fd_apply<TTD_EPI_DGRAD, ACT_ELU, false>(P, m, n0, v, S0, keep, inv_keep, drop_thresh); break;
+          default: epi_fd_apply<TTD_EPI_DGRAD, ACT_ELU, true>(P, m, n0, v, S0, keep, inv_keep, drop_thresh); break;
         }
+        S0 = S1;
       }
     }
   }
@@ -499,10 +519,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_group_kernel(const __grid_co
     }
   } else if (warp >= 4) {
     // ===================== epilogue: TMEM -> registers -> global =====================
-    mbar_wait(tmem_full_bar, 0);
-    tc_fence_after();
     const EpiCtx E{g.seed_lo, g.seed_hi, g.step_ptr, smem};
-    run_epilogue(P, E, tmem_base, m0, nbase, warp, lane);
+    run_epilogue(P, E, tmem_base, m0, nbase, warp, lane, tmem_full_bar, 0);
   }
 
   tc_fence_before();
@@ -853,10 +871,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_chain_kernel(const GemmProbl
         }
         umma_commit(done_bar);
       } else if (warp >= 4) {
-        mbar_wait(done_bar, ph);
         if (tr && threadIdx.x == 128) tr[2] = globaltimer_ns();
-        tc_fence_after();
-        run_epilogue(P, E, tmem_base, m0, nbase, warp, lane);
+        run_epilogue(P, E, tmem_base, m0, nbase, warp, lane, done_bar, ph);
         tc_fence_before();
         if (tr && threadIdx.x == 128) tr[3] = globaltimer_ns();
       }
