@@ -154,7 +154,7 @@ def run(args) -> int:
     cfg = TrainConfig(job_name="worker", task_id=rank, worker_hosts=hosts, ps_hosts="127.0.0.1:2221",
                       model=spec["model"], sync_replicas=spec["sync_replicas"], batch_size=args.batch,
                       training_steps=10**9, seed=1234, save_checkpoint_secs=None, cuda_graph=not args.no_graph,
-                      pdl=not args.no_pdl, fused_tail=not args.no_fused_tail)
+                      pdl=not args.no_pdl, fused_tail=args.fused_tail)
     trainer = GpuTrainer(cfg, device_index=local_rank, comm=comm)
     trainer.initialize()
     B, F = cfg.batch_size, cfg.input_dim
@@ -280,7 +280,7 @@ def main() -> int:
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-pdl", action="store_true")
-    ap.add_argument("--no-fused-tail", action="store_true", help="one GEMM launch per layer instead of the chain kernel")
+    ap.add_argument("--fused-tail", action="store_true", help="run the narrow layers as one chain-kernel launch")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

@@ -93,7 +93,8 @@ class TrainConfig:
     prefetch: int = 0  # >0: background reader threads (README "ReadByQueue" variant)
     cuda_graph: bool = True
     pdl: bool = True  # programmatic dependent launch between the kernels of a step
-    fused_tail: bool = True  # narrow layers behind the first: forward + loss + backward in ONE kernel launch
+    fused_tail: bool = False  # narrow layers behind the first in ONE launch (measured slower than a launch per
+    # layer on B200: one CTA serialises epilogues that separate launches spread over several CTAs; see profiles/)
     tail_impl: str = "chain"  # chain: single-CTA tcgen05 chain kernel | cluster: fp32 CUDA-core cluster kernel
     pull_fused: bool = True  # sync multi-GPU: fetch W1 from its owners inside the first GEMM (K3) instead of broadcasting it
     write_events: bool = True

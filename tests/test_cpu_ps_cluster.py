@@ -67,7 +67,7 @@ def test_async_one_ps_two_workers(tmp_path):
         assert rc == 0, (k, out[-3000:])
     (s0, g0), (s1, g1) = _final(outs[("worker", 0)][1]), _final(outs[("worker", 1)][1])
     assert g0 >= 300 and g1 >= 300
-    assert s0 + s1 >= 300 and s0 < 300 and s1 < 300  # shared global step: neither worker did all the steps
+    assert 300 <= s0 + s1 <= 304  # the global steps are SHARED: together the workers run ~300 local steps, not 600
     assert "session started" in outs[("worker", 0)][1]
     l0 = _losses(outs[("worker", 0)][1])
     assert l0 and l0[-1] < 1.0  # learned something from 2.30

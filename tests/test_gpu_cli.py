@@ -68,4 +68,4 @@ def test_two_gpu_async_replicas_cli(tmp_path):
     assert rc == 0, out[-3000:]
     fin = _finals(out)
     assert len(fin) == 2 and all(g >= 400 for _, g in fin)
-    assert sum(s for s, _ in fin) >= 400 and all(s < 400 for s, _ in fin)  # the global steps are shared (:220-222)
+    assert 400 <= sum(s for s, _ in fin) <= 408  # the global steps are shared (:220-222): ~400 local steps in total

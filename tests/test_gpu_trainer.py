@@ -70,10 +70,10 @@ def test_graph_replay_equals_eager_and_learns():
     a = GpuTrainer(_cfg(cuda_graph=True))
     b = GpuTrainer(_cfg(cuda_graph=False))
     a.initialize(), b.initialize()
-    assert a.launches_per_step == 5   # prep + first-layer fwd + fused tail + first-layer wgrad + update
-    c = GpuTrainer(_cfg(cuda_graph=False, fused_tail=False))
+    assert a.launches_per_step == 12  # prep + 5 fwd + 5 bwd + update: every layer is its own GEMM launch
+    c = GpuTrainer(_cfg(cuda_graph=False, fused_tail=True))
     c.initialize()
-    assert c.launches_per_step == 12  # prep + 5 fwd + 5 bwd + update when every layer is its own GEMM
+    assert c.launches_per_step == 5   # prep + first-layer fwd + chain kernel + first-layer wgrad + update
     c.close()
     la = lb = None
     first = None
