@@ -69,6 +69,17 @@ class GpuTrainer:
                                        tail_groups=tail)
             self.model = self._build_model()
             self._pinned_state = torch.zeros(self.RING, 8, dtype=torch.int64).pin_memory()
+            # Host-fed batches land in a two-slot device pool; the captured step picks slot local_step % 2 on the
+            # device, so the H2D copy of batch s+1 (copy stream) overlaps the compute of batch s (one graph).
+            B, F = self.model.x.shape
+            self._feed_x = torch.zeros(2, B, F, device=self.device, dtype=torch.float32)
+            self._feed_y = torch.zeros(2, B, device=self.device, dtype=torch.int64)
+            self.model.set_device_dataset(self._feed_x, self._feed_y)
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self._ev_ready = [torch.cuda.Event() for _ in range(2)]
+        self._ev_free = [torch.cuda.Event() for _ in range(2)]
+        self._fed_slot: Optional[int] = None
+        self._user_pool = False
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._launches_per_step = 0
         self._slot = 0
@@ -118,6 +129,8 @@ class GpuTrainer:
             if self.comm is not None:
                 self.comm.reset_flags(self.store)
                 self.comm.barrier()
+        self._steps_enqueued = 0  # mirrors the device's local_step (which slot of the feed pool a step reads)
+        self._fed_slot = None
         if self.cfg.cuda_graph:
             self._capture()
         self._initialized = True
@@ -132,6 +145,10 @@ class GpuTrainer:
         """Switch between a device-resident data set ([P,B,F] / [P,B], batch picked on the device from the
         local step) and host-fed batches (``None``); the step graph is re-captured for the new source."""
         self.stream.synchronize()
+        self.copy_stream.synchronize()
+        self._user_pool = x_pool is not None
+        if x_pool is None:
+            x_pool, labels_pool = self._feed_x, self._feed_y
         self.model.set_device_dataset(x_pool, labels_pool)
         if self._graph is not None:
             self._capture()
@@ -142,21 +159,39 @@ class GpuTrainer:
         return self._launches_per_step
 
     def load_batch(self, x, y) -> Tuple[int, int]:
-        """Host -> device copy of one batch on the trainer's stream; returns (bytes_x, bytes_y)."""
+        """Host -> device copy of the batch for the NEXT step, on the copy stream, into the feed-pool slot that
+        step will read; returns (bytes_x, bytes_y). Pinned sources make the copy asynchronous."""
         if isinstance(x, np.ndarray):
             x = torch.from_numpy(x)
         if isinstance(y, np.ndarray):
             y = torch.from_numpy(y)
-        self.model.x.copy_(x.view(self.model.x.shape), non_blocking=True)
-        self.model.labels.copy_(y, non_blocking=True)
+        slot = self._steps_enqueued % 2
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self._ev_free[slot])  # the step that last read this slot is done with it
+            self._feed_x[slot].copy_(x.view(self._feed_x[slot].shape), non_blocking=True)
+            self._feed_y[slot].copy_(y, non_blocking=True)
+            self._ev_ready[slot].record(self.copy_stream)
+        self._fed_slot = slot
         return x.numel() * x.element_size(), y.numel() * y.element_size()
 
+    def wait_batch(self) -> Optional[int]:
+        """Make the current stream wait for the batch fed by ``load_batch``; returns its feed-pool slot."""
+        slot = self._fed_slot
+        if slot is not None:
+            torch.cuda.current_stream(self.device).wait_event(self._ev_ready[slot])
+        return slot
+
     def run_step(self) -> None:
-        """Enqueue one training step on the batch currently in the static input buffers."""
+        """Enqueue one training step (on the batch fed for it, or on the device-resident data set)."""
+        stream = torch.cuda.current_stream(self.device)
+        slot = self.wait_batch()
         if self._graph is not None:
             self._graph.replay()
         else:
             self.model.launch_step(sync=self.sync)
+        if slot is not None:
+            self._ev_free[slot].record(stream)
+            self._fed_slot = None
         self._steps_enqueued += 1
 
     def fetch_async(self) -> int:

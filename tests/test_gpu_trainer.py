@@ -45,6 +45,7 @@ def test_step_gradients_match_autograd(act, tail):
     vars_ = tr.export_variables()
     with torch.cuda.stream(tr.stream):
         tr.load_batch(xs, ys)
+        tr.wait_batch()
         tr.store.state.view(torch.float32)[4:6] = 0
         tr.model.launch_forward_backward()
     tr.synchronize()
@@ -177,6 +178,7 @@ def test_lenet_gradients_match_autograd_and_it_learns():
     xs, ys = ds.next_batch(128)
     with torch.cuda.stream(tr.stream):
         tr.load_batch(xs, ys)
+        tr.wait_batch()
         tr.store.state.view(torch.float32)[4:6] = 0
         tr.model.launch_forward_backward()
     tr.synchronize()
