@@ -55,6 +55,7 @@ struct PeerInfo {
   long long bounds[kMaxPeers + 1];   // owner k holds flat range [bounds[k], bounds[k+1])
   TtdStepState* state0;              // step state of the owner of global_step (shard 0)
   int n_owners;
+  int trace_all;                     // diagnostic: phase clocks as the maximum over all CTAs (TtdPeers.reserved bit0)
 };
 
 enum { kInit = 0, kRefresh = 1, kUpdate = 2, kAsyncPull = 3, kAsyncPush = 4 };
@@ -163,6 +164,123 @@ __device__ __forceinline__ void broadcast_store(const PeerInfo& pi, void* local_
     if (q < pi.n_copies) *reinterpret_cast<VecT*>(reinterpret_cast<char*>(local_ptr) + pi.copy_delta[q]) = v;
 }
 
+// Gradient gather: ROWS x N loads of one thread issued back to back as straight-line code (no predicates, no
+// branches), every result in its own register, summed afterwards. With predicated loads and the adds in
+// between, ptxas keeps at most three loads in flight and the scoreboard makes the rest queue behind them — one
+// NVLink round trip per group (measured: 18 us for 8 rows x 2 replicas, 50 us for 8 x 8).
+template <int N, int ROWS>
+__device__ __forceinline__ void gather_f32(const PeerInfo& pi, long long base, const int* idx, float* out) {
+  float t[ROWS][N];
+#pragma unroll
+  for (int r = 0; r < ROWS; ++r)
+#pragma unroll
+    for (int q = 0; q < N; ++q) t[r][q] = __ldcv(pi.grads[q] + base + idx[r]);  // written by another GPU: never L1
+#pragma unroll
+  for (int r = 0; r < ROWS; ++r) {
+    float a = t[r][0];
+#pragma unroll
+    for (int q = 1; q < N; ++q) a += t[r][q];
+    out[r] = a;
+  }
+}
+template <int N>
+__device__ __forceinline__ void gather_rows8(const PeerInfo& pi, long long base, const int* idx, float* out) {
+  constexpr int CH = N <= 2 ? 8 : (N <= 4 ? 4 : 2);  // at most 16 loads in flight per thread (64-register cap)
+#pragma unroll
+  for (int b = 0; b < 8; b += CH) gather_f32<N, CH>(pi, base, idx + b, out + b);
+}
+template <int N, int U>
+__device__ __forceinline__ void gather_vec(const PeerInfo& pi, const long long* idx, float4* out) {
+  float4 t[U][N];
+#pragma unroll
+  for (int u = 0; u < U; ++u)
+#pragma unroll
+    for (int q = 0; q < N; ++q) t[u][q] = __ldcv(reinterpret_cast<const float4*>(pi.grads[q] + idx[u]));
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    float4 a = t[u][0];
+#pragma unroll
+    for (int q = 1; q < N; ++q) { a.x += t[u][q].x; a.y += t[u][q].y; a.z += t[u][q].z; a.w += t[u][q].w; }
+    out[u] = a;
+  }
+}
+template <int N>
+__device__ __forceinline__ void gather_vec2(const PeerInfo& pi, const long long* idx, float4* out) {
+  if constexpr (N <= 4) {  // at most 8 x 16 bytes in flight per thread (the kernel is capped at 64 registers)
+    gather_vec<N, 2>(pi, idx, out);
+  } else {
+    gather_vec<N, 1>(pi, idx, out);
+    gather_vec<N, 1>(pi, idx + 1, out + 1);
+  }
+}
+#define TTD_GATHER_SWITCH(n, CALL)                         \
+  switch (n) {                                             \
+    case 1: CALL(1); break;                                \
+    case 2: CALL(2); break;                                \
+    case 3: CALL(3); break;                                \
+    case 4: CALL(4); break;                                \
+    case 5: CALL(5); break;                                \
+    case 6: CALL(6); break;                                \
+    case 7: CALL(7); break;                                \
+    default: CALL(8); break;                               \
+  }
+
+__device__ __forceinline__ float multimem_ld_reduce_f32(const float* mc_addr) {
+  float r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(r) : "l"(mc_addr) : "memory");
+  return r;
+}
+// one fp32 element to every replica
+__device__ __forceinline__ void broadcast_store_f32(const PeerInfo& pi, float* local_ptr, float v) {
+  if (pi.n_copies <= 1) {
+    *local_ptr = v;
+  } else if (pi.mc_delta != 0) {
+    asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(reinterpret_cast<char*>(local_ptr) + pi.mc_delta),
+                 "f"(v)
+                 : "memory");
+  } else {
+#pragma unroll
+    for (int q = 0; q < kMaxPeers; ++q)
+      if (q < pi.n_copies) *reinterpret_cast<float*>(reinterpret_cast<char*>(local_ptr) + pi.copy_delta[q]) = v;
+  }
+}
+// One bf16 element per lane, neighbouring lanes at neighbouring addresses, to every replica. Lanes pair up
+// (the one at the 4-byte aligned address stores both halves) so a replica receives one 4-byte store per pair —
+// one multimem.st when the fabric has a multicast alias — instead of two 2-byte stores per replica.
+// Must be called by all 32 lanes of the warp.
+__device__ __forceinline__ void broadcast_store_bf16_lane(const PeerInfo& pi, __nv_bfloat16* dst, float val, bool on,
+                                                          bool local_only) {
+  const int lane = threadIdx.x & 31;
+  const float nval = __shfl_down_sync(0xffffffffu, val, 1);
+  const bool n_on = __shfl_down_sync(0xffffffffu, on ? 1 : 0, 1) != 0 && lane < 31;
+  const bool p_on = __shfl_up_sync(0xffffffffu, on ? 1 : 0, 1) != 0 && lane > 0;
+  const bool aligned = (reinterpret_cast<uintptr_t>(dst) & 3) == 0;
+  if (!on) return;
+  if (aligned && n_on) {
+    const uint32_t pk = pack_bf16x2(val, nval);
+    if (local_only || pi.n_copies <= 1) {
+      *reinterpret_cast<uint32_t*>(dst) = pk;
+    } else if (pi.mc_delta != 0) {
+      asm volatile("multimem.st.relaxed.sys.global.bf16x2 [%0], %1;" ::"l"(reinterpret_cast<char*>(dst) + pi.mc_delta),
+                   "r"(pk)
+                   : "memory");
+    } else {
+#pragma unroll
+      for (int q = 0; q < kMaxPeers; ++q)
+        if (q < pi.n_copies) *reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(dst) + pi.copy_delta[q]) = pk;
+    }
+    return;
+  }
+  if (!aligned && p_on) return;  // the lane below stored this element with its own
+  const __nv_bfloat16 b = __float2bfloat16(val);
+  if (local_only || pi.n_copies <= 1) {
+    *dst = b;
+    return;
+  }
+  for (int q = 0; q < pi.n_copies; ++q)
+    *reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(dst) + pi.copy_delta[q]) = b;
+}
+
 __device__ __forceinline__ float trunc_normal(uint64_t seed, uint64_t idx) {
   // Philox + Box-Muller, resampled until |z| <= 2 (TF truncated_normal), deterministic in (seed, idx)
   for (uint32_t attempt = 0; attempt < 16; ++attempt) {
@@ -193,7 +311,9 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
   __shared__ unsigned long long s_lstep;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint64_t k_start = (MODE == kUpdate && blockIdx.x == 0 && threadIdx.x == 0) ? globaltimer_ns() : 0;
+  // TtdPeers.reserved bit0: diagnostic trace over ALL CTAs (maximum per phase; the host zeroes the slots first)
+  const bool trace_all = MODE == kUpdate && (pi.trace_all != 0);
+  const uint64_t k_start = (MODE == kUpdate && (blockIdx.x == 0 || trace_all) && threadIdx.x == 0) ? globaltimer_ns() : 0;
 
   if (MODE == kUpdate || MODE == kAsyncPull || MODE == kAsyncPush) {
     if (threadIdx.x == 0) {
@@ -220,10 +340,14 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
   const float lr = s_lr, ema_d = s_ema_d;
   // phase clock of CTA 0 (ns since kernel start) for the push/pull trace: st->reserved[0..4] =
   // {after barrier-in, after the gradient loads of its first tile, after its last tile, after barrier-out, #tiles}
-  const bool trace = (MODE == kUpdate) && blockIdx.x == 0 && threadIdx.x == 0;
+  const bool trace = (MODE == kUpdate) && (blockIdx.x == 0 || trace_all) && threadIdx.x == 0;
   const uint64_t k_t0 = k_start;
   uint32_t tr_loads = 0, tr_ntiles = 0;
-  if (trace) st->reserved[0] = static_cast<uint32_t>(globaltimer_ns() - k_start);
+  if (trace) {
+    const uint32_t v = static_cast<uint32_t>(globaltimer_ns() - k_start);
+    if (trace_all) atomicMax(&st->reserved[0], v);
+    else st->reserved[0] = v;
+  }
 
   const int total_tiles = vt.tile_begin[vt.n];
   for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -250,7 +374,7 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
       const int c = c0 + 4 * cg;
       const bool use_ema = ema != nullptr && h.ema_decay > 0.0f;
       float4 g4[2], w4[2], s4[2];
-      long long idx2[2];
+      long long idx2[2], idx_ld[2];
       bool ok2[2];
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
@@ -259,21 +383,21 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
         const bool ok = r < R && c < C && idx >= lo && idx + 3 < hi;
         idx2[u] = idx;
         ok2[u] = ok;
-        g4[u] = w4[u] = s4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (ok) {
-          if (pi.grads_mc != nullptr) {
-            g4[u] = multimem_ld_reduce_f32x4(pi.grads_mc + idx);
-          } else {
+        idx_ld[u] = ok ? idx : V.offset;  // lanes without work load a valid address and drop the value
+      }
+      // every load of the thread is issued before anything consumes one (see gather_f32)
+      if (pi.grads_mc != nullptr) {
 #pragma unroll
-            for (int q = 0; q < kMaxPeers; ++q)
-              if (q < pi.n_grads) {
-                const float4 t4 = ld_cv_f32x4(pi.grads[q] + idx);
-                g4[u].x += t4.x; g4[u].y += t4.y; g4[u].z += t4.z; g4[u].w += t4.w;
-              }
-          }
-          w4[u] = *reinterpret_cast<const float4*>(w + idx);
-          if (use_ema) s4[u] = *reinterpret_cast<const float4*>(ema + idx);
-        }
+        for (int u = 0; u < 2; ++u) g4[u] = multimem_ld_reduce_f32x4(pi.grads_mc + idx_ld[u]);
+      } else {
+#define TTD_CALL(N) gather_vec2<N>(pi, idx_ld, g4)
+        TTD_GATHER_SWITCH(pi.n_grads, TTD_CALL)
+#undef TTD_CALL
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        w4[u] = *reinterpret_cast<const float4*>(w + idx_ld[u]);
+        s4[u] = use_ema ? *reinterpret_cast<const float4*>(ema + idx_ld[u]) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
       if (trace) {
         if (tr_ntiles == 0) {
@@ -383,25 +507,19 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
     }
     // phase 1: addresses + every load of this thread's four elements issued back to back, so the NVLink
     // round trips to the peers' gradient buffers overlap instead of queueing behind one another
-    long long idxs[kTileR / 8];
-    bool oks[kTileR / 8];
+    uint32_t okmask = 0;
     float gsum[kTileR / 8], wold[kTileR / 8], sold[kTileR / 8];
+    int rel_ld[kTileR / 8];  // element index relative to the group's offset (a group holds < 2^31 elements)
+    static_assert(kTileR / 8 == 8, "gather_rows8 handles eight rows per thread");
 #pragma unroll
     for (int rr = 0; rr < kTileR / 8; ++rr) {
       const int r = r0 + warp + 8 * rr, c = c0 + lane;
       const long long idx = V.offset + static_cast<long long>(r) * C + c;
       const bool ok = r < R && c < C && idx >= lo && idx < hi;
-      idxs[rr] = idx;
-      oks[rr] = ok;
+      okmask |= (ok ? 1u : 0u) << rr;
       gsum[rr] = wold[rr] = sold[rr] = 0.0f;
-      if (MODE == kUpdate && ok) {
-        float g = 0.0f;
-#pragma unroll
-        for (int q = 0; q < kMaxPeers; ++q)
-          if (q < pi.n_grads) g += __ldcv(pi.grads[q] + idx);  // written by another GPU: never a stale L1 line
-        gsum[rr] = g;
-        wold[rr] = w[idx];
-        if (ema != nullptr && h.ema_decay > 0.0f) sold[rr] = ema[idx];
+      if (MODE == kUpdate) {
+        rel_ld[rr] = ok ? static_cast<int>(idx - V.offset) : 0;  // lanes without work load a valid address and drop it
       } else if (MODE == kRefresh && ok) {
         wold[rr] = w[idx];
       } else if (MODE == kAsyncPull && ok) {
@@ -410,6 +528,22 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
       } else if (MODE == kAsyncPush && ok) {
         gsum[rr] = pi.grads[0][idx];
         wold[rr] = w[idx];  // the snapshot this gradient was computed with
+      }
+    }
+    if (MODE == kUpdate) {
+      if (pi.grads_mc != nullptr) {  // the switch adds the replicas' values: one request per element, not n
+#pragma unroll
+        for (int rr = 0; rr < kTileR / 8; ++rr) gsum[rr] = multimem_ld_reduce_f32(pi.grads_mc + V.offset + rel_ld[rr]);
+      } else {
+#define TTD_CALL(N) gather_rows8<N>(pi, V.offset, rel_ld, gsum)
+        TTD_GATHER_SWITCH(pi.n_grads, TTD_CALL)
+#undef TTD_CALL
+      }
+      const bool use_ema = ema != nullptr && h.ema_decay > 0.0f;
+#pragma unroll
+      for (int rr = 0; rr < kTileR / 8; ++rr) {
+        wold[rr] = w[V.offset + rel_ld[rr]];
+        sold[rr] = use_ema ? ema[V.offset + rel_ld[rr]] : 0.0f;
       }
     }
     if (trace) {
@@ -427,8 +561,8 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
     for (int rr = 0; rr < kTileR / 8; ++rr) {
       const int rl = warp + 8 * rr;
       const int r = r0 + rl, c = c0 + lane;
-      const bool ok = oks[rr];
-      const long long idx = idxs[rr];
+      const bool ok = (okmask >> rr) & 1u;
+      const long long idx = V.offset + static_cast<long long>(r) * C + c;
       float val = 0.0f;
       if (ok) {
         if (MODE == kInit) {
@@ -465,25 +599,13 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
           w[idx] = val;
           if (ema != nullptr && h.ema_decay > 0.0f) ema[idx] = sold[rr] - (1.0f - ema_d) * (sold[rr] - val);
         }
-        if (MODE != kAsyncPush && V.bias_c != nullptr && r == V.rows) {
-          for (int q = 0; q < pi.n_copies; ++q) {
-            float* dst = reinterpret_cast<float*>(reinterpret_cast<char*>(V.bias_c) + pi.copy_delta[q]);
-            dst[c] = val;
-          }
-        }
-        if (MODE != kAsyncPush && V.w_f32 != nullptr && r < V.rows) {
-          for (int q = 0; q < pi.n_copies; ++q)
-            *reinterpret_cast<float*>(reinterpret_cast<char*>(V.w_f32 + static_cast<long long>(r) * V.ld_f32 + c) +
-                                      pi.copy_delta[q]) = val;
-        }
-        if (MODE != kAsyncPush && V.w_rm != nullptr && r < V.rows) {
-          const __nv_bfloat16 b = __float2bfloat16(val);
-          for (int q = 0; q < pi.n_copies; ++q) {
-            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(V.w_rm) + pi.copy_delta[q]);
-            dst[static_cast<long long>(r) * V.ld_rm + c] = b;
-          }
-        }
+        if (MODE != kAsyncPush && V.bias_c != nullptr && r == V.rows) broadcast_store_f32(pi, V.bias_c + c, val);
+        if (MODE != kAsyncPush && V.w_f32 != nullptr && r < V.rows)
+          broadcast_store_f32(pi, V.w_f32 + static_cast<long long>(r) * V.ld_f32 + c, val);
       }
+      if (MODE != kAsyncPush && V.w_rm != nullptr)  // (whole warp: the lanes pair up)
+        broadcast_store_bf16_lane(pi, static_cast<__nv_bfloat16*>(V.w_rm) + static_cast<long long>(r) * V.ld_rm + c, val,
+                                  ok && r < V.rows, false);
       tile[rl][lane] = val;
       tile_ok[rl][lane] = (ok && MODE != kAsyncPush) ? 1 : 0;
     }
@@ -496,9 +618,7 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
           const int cl = warp + 8 * cc, rl = lane + 32 * half;
           const int c = c0 + cl, r = r0 + rl;
           if (tile_ok[rl][cl] && r < V.rows && c < C)
-            for (int q = 0; q < pi.n_copies; ++q)
-              *reinterpret_cast<float*>(reinterpret_cast<char*>(V.wt_f32 + static_cast<long long>(c) * V.ld_tf32 + r) +
-                                        pi.copy_delta[q]) = tile[rl][cl];
+            broadcast_store_f32(pi, V.wt_f32 + static_cast<long long>(c) * V.ld_tf32 + r, tile[rl][cl]);
         }
       }
     }
@@ -509,16 +629,10 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
         for (int cc = 0; cc < kTile / 8; ++cc) {
           const int cl = warp + 8 * cc, rl = lane + 32 * half;
           const int c = c0 + cl, r = r0 + rl;
-          if (tile_ok[rl][cl] && r < V.rows && c < C) {
-            const __nv_bfloat16 b = __float2bfloat16(tile[rl][cl]);
-            for (int q = 0; q < pi.n_copies; ++q) {
-              // flag bit0: consumers fetch this operand from its owner by TMA (pull-fused GEMM), so the
-              // transposed copy is NOT broadcast; only the owner's own buffer is refreshed
-              if ((V.reserved & 1) && pi.copy_delta[q] != 0) continue;
-              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(V.w_t) + pi.copy_delta[q]);
-              dst[static_cast<long long>(c) * V.ld_t + r] = b;
-            }
-          }
+          // flag bit0: consumers fetch this operand from its owner by TMA (pull-fused GEMM), so the
+          // transposed copy is NOT broadcast; only the owner's own buffer is refreshed
+          broadcast_store_bf16_lane(pi, static_cast<__nv_bfloat16*>(V.w_t) + static_cast<long long>(c) * V.ld_t + r,
+                                    tile[rl][cl], tile_ok[rl][cl] && r < V.rows && c < C, (V.reserved & 1) != 0);
         }
       }
     }
@@ -530,10 +644,18 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
       replica_barrier<true>(pi, static_cast<uint32_t>(2 * s_lstep + 2));
     }
     if (trace) {
-      st->reserved[1] = tr_loads;
-      st->reserved[2] = tr_tiles_done;
-      st->reserved[3] = static_cast<uint32_t>(globaltimer_ns() - k_t0);
-      st->reserved[4] = tr_ntiles;
+      const uint32_t t_out = static_cast<uint32_t>(globaltimer_ns() - k_t0);
+      if (trace_all) {
+        atomicMax(&st->reserved[1], tr_loads);
+        atomicMax(&st->reserved[2], tr_tiles_done);
+        atomicMax(&st->reserved[3], t_out);
+        atomicMax(&st->reserved[4], tr_ntiles);
+      } else {
+        st->reserved[1] = tr_loads;
+        st->reserved[2] = tr_tiles_done;
+        st->reserved[3] = t_out;
+        st->reserved[4] = tr_ntiles;
+      }
     }
     // the last block to finish advances the step counters (nobody reads them any more in this launch)
     __shared__ unsigned int s_last;
@@ -661,6 +783,7 @@ extern "C" int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars, in
   pi.n_copies = peers->n_copies;
   pi.rank = peers->rank;
   pi.barrier = peers->barrier;
+  pi.trace_all = peers->reserved & 1;
   int grid = grid_for(vt.tile_begin[vt.n] > 0 ? vt.tile_begin[vt.n] : 1);
   if (pi.barrier) {
     // blocks of different replicas wait on one another: all of them must be resident at once

@@ -152,7 +152,7 @@ typedef struct TtdPeers {
   int32_t n_grads, n_copies, rank;
   int32_t barrier;                     /* 1: bracket the update with cross-replica barriers */
   int32_t grid;                        /* barrier mode: CTA count, identical on all replicas, <= 592 (all co-resident) */
-  int32_t reserved;
+  int32_t reserved;                    /* bit0: diagnostic phase clocks as the max over all CTAs (host zeroes TtdStepState.reserved) */
 } TtdPeers;
 
 /* Fused gradient push over the flat range [lo, hi) owned by the caller:

@@ -58,6 +58,19 @@ def main():
     res["trace_ns"] = dict(after_barrier_in=trace[0], first_tile_loads=trace[1], tiles_done=trace[2],
                            after_barrier_out=trace[3], tiles=trace[4])
 
+    # slowest CTA of every rank, phase by phase (TtdPeers.reserved bit0), one eager launch
+    st._peers.reserved = 1
+    comm.barrier()
+    with torch.cuda.stream(tr.stream):
+        st.state.view(torch.int32)[10:16] = 0
+        st.apply_update()
+    tr.synchronize()
+    mine = st.state.view(torch.int32)[10:15].clone()
+    allr = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(allr, mine)
+    res["trace_max_over_ctas_ns"] = {f"rank{r}": t.tolist() for r, t in enumerate(allr)}
+    st._peers.reserved = 0
+
     def no_bcast():
         st._peers.n_copies = 1
     res.update([timeit("no_broadcast", no_bcast)])
