@@ -214,9 +214,7 @@ def run(args) -> int:
 
     def e2e_step(i):
         j = i % host_pool
-        trainer.load_batch(hx[j], hy[j])
-        trainer.run_step()
-        slots.append(trainer.fetch_async())
+        slots.append(trainer.step_async(hx[j], hy[j]))  # H2D (copy stream) + step + 64-byte D2H, one native call
 
     with torch.cuda.stream(trainer.stream):
         for i in range(args.warmup):

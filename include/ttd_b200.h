@@ -249,6 +249,20 @@ int ttd_conv_pool_bwd(const TtdConvDesc* d, const void* dzp, int64_t ld_dzp, int
 /* cudaMemcpyAsync(device -> device) on `stream`; lets Python snapshot peer-mapped shards for checkpoints. */
 int ttd_copy_d2d(void* dst, const void* src, uint64_t nbytes, void* stream);
 
+/* ---- step feeder: the host side of a training step in one native call (reference: the C++ session run loop
+ * behind mon_sess.run, distribute_training.py:225). Host batches are copied on `copy_stream` into a two-slot
+ * device pool (slot = step & 1; the captured step picks local_step % 2 on the device); events order the copy
+ * behind the slot's last reader and the step behind the copy. All handles are raw CUDA handles. */
+void* ttd_feeder_create(void* compute_stream, void* copy_stream, void* x_slot0, void* x_slot1, void* y_slot0,
+                        void* y_slot1, size_t x_bytes, size_t y_bytes);
+void ttd_feeder_destroy(void* feeder);
+int ttd_feeder_feed(void* feeder, const void* host_x, const void* host_y, uint64_t step);
+int ttd_feeder_before_step(void* feeder); /* returns the fed slot or -1; < -1 never; -1 with an error set on failure */
+int ttd_feeder_after_step(void* feeder);
+/* feed (host_x != NULL) + cudaGraphLaunch(graph_exec) + optional 64-byte TtdStepState read-back to pinned memory */
+int ttd_feeder_step(void* feeder, void* graph_exec, const void* host_x, const void* host_y, uint64_t step,
+                    const void* state_dev, void* state_host);
+
 /* The same update for hosts that may not allocate device memory (no counterpart in the reference).
  * Meant for callers embedded in a process that has given all of HBM to its own arena, or that cannot
  * afford the device-wide synchronisation of cudaMalloc/cudaFree inside their loop. One gradient source,

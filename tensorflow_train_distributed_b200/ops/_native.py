@@ -192,6 +192,18 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.ttd_prep_input_ex.restype = C.c_int
     lib.ttd_prep_input_ex.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
                                       C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+    lib.ttd_feeder_create.restype = C.c_void_p
+    lib.ttd_feeder_create.argtypes = [C.c_void_p] * 6 + [C.c_size_t, C.c_size_t]
+    lib.ttd_feeder_destroy.restype = None
+    lib.ttd_feeder_destroy.argtypes = [C.c_void_p]
+    lib.ttd_feeder_feed.restype = C.c_int
+    lib.ttd_feeder_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
+    lib.ttd_feeder_before_step.restype = C.c_int
+    lib.ttd_feeder_before_step.argtypes = [C.c_void_p]
+    lib.ttd_feeder_after_step.restype = C.c_int
+    lib.ttd_feeder_after_step.argtypes = [C.c_void_p]
+    lib.ttd_feeder_step.restype = C.c_int
+    lib.ttd_feeder_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
     lib.ttd_init_params.restype = C.c_int
     lib.ttd_init_params.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(VarDesc), C.c_int, C.c_uint64, C.c_void_p]
     lib.ttd_refresh_copies.restype = C.c_int

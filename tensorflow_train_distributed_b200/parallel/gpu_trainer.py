@@ -76,9 +76,14 @@ class GpuTrainer:
             self._feed_y = torch.zeros(2, B, device=self.device, dtype=torch.int64)
             self.model.set_device_dataset(self._feed_x, self._feed_y)
         self.copy_stream = torch.cuda.Stream(device=self.device)
-        self._ev_ready = [torch.cuda.Event() for _ in range(2)]
-        self._ev_free = [torch.cuda.Event() for _ in range(2)]
-        self._fed_slot: Optional[int] = None
+        self.lib = N.load()
+        self._feeder = self.lib.ttd_feeder_create(
+            self.stream.cuda_stream, self.copy_stream.cuda_stream, self._feed_x[0].data_ptr(), self._feed_x[1].data_ptr(),
+            self._feed_y[0].data_ptr(), self._feed_y[1].data_ptr(), self._feed_x[0].numel() * 4, self._feed_y[0].numel() * 8)
+        if not self._feeder:
+            raise N.NativeError("ttd_feeder_create failed: " + self.lib.ttd_last_error().decode(errors="replace"))
+        self._host_keep = [None, None]
+        self._graph_exec: Optional[int] = None
         self._user_pool = False
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._launches_per_step = 0
@@ -130,7 +135,6 @@ class GpuTrainer:
                 self.comm.reset_flags(self.store)
                 self.comm.barrier()
         self._steps_enqueued = 0  # mirrors the device's local_step (which slot of the feed pool a step reads)
-        self._fed_slot = None
         if self.cfg.cuda_graph:
             self._capture()
         self._initialized = True
@@ -140,6 +144,7 @@ class GpuTrainer:
         with torch.cuda.graph(g, stream=self.stream):
             self.model.launch_step(sync=self.sync)
         self._graph = g
+        self._graph_exec = int(g.raw_cuda_graph_exec())  # launched by the native feeder (ttd_feeder_step)
 
     def use_device_dataset(self, x_pool, labels_pool) -> None:
         """Switch between a device-resident data set ([P,B,F] / [P,B], batch picked on the device from the
@@ -158,41 +163,64 @@ class GpuTrainer:
     def launches_per_step(self) -> int:
         return self._launches_per_step
 
+    def _host_batch(self, x, y):
+        x = torch.as_tensor(x)
+        y = torch.as_tensor(y)
+        if x.dtype != torch.float32 or not x.is_contiguous():
+            x = x.to(torch.float32).contiguous()
+        if y.dtype != torch.int64 or not y.is_contiguous():
+            y = y.to(torch.int64).contiguous()
+        if x.numel() != self._feed_x[0].numel() or y.numel() != self._feed_y[0].numel():
+            raise ValueError(f"batch of shape {tuple(x.shape)} / {tuple(y.shape)} does not match the model's "
+                             f"{tuple(self._feed_x[0].shape)} / {tuple(self._feed_y[0].shape)}")
+        return x, y
+
     def load_batch(self, x, y) -> Tuple[int, int]:
         """Host -> device copy of the batch for the NEXT step, on the copy stream, into the feed-pool slot that
         step will read; returns (bytes_x, bytes_y). Pinned sources make the copy asynchronous."""
-        if isinstance(x, np.ndarray):
-            x = torch.from_numpy(x)
-        if isinstance(y, np.ndarray):
-            y = torch.from_numpy(y)
+        x, y = self._host_batch(x, y)
         slot = self._steps_enqueued % 2
-        with torch.cuda.stream(self.copy_stream):
-            self.copy_stream.wait_event(self._ev_free[slot])  # the step that last read this slot is done with it
-            self._feed_x[slot].copy_(x.view(self._feed_x[slot].shape), non_blocking=True)
-            self._feed_y[slot].copy_(y, non_blocking=True)
-            self._ev_ready[slot].record(self.copy_stream)
-        self._fed_slot = slot
+        N.check(self.lib.ttd_feeder_feed(self._feeder, x.data_ptr(), y.data_ptr(), self._steps_enqueued), "ttd_feeder_feed")
+        self._host_keep[slot] = (x, y)  # the copy may still be reading them
         return x.numel() * x.element_size(), y.numel() * y.element_size()
 
     def wait_batch(self) -> Optional[int]:
-        """Make the current stream wait for the batch fed by ``load_batch``; returns its feed-pool slot."""
-        slot = self._fed_slot
-        if slot is not None:
-            torch.cuda.current_stream(self.device).wait_event(self._ev_ready[slot])
-        return slot
+        """Make the compute stream wait for the batch fed by ``load_batch``; returns its feed-pool slot."""
+        slot = self.lib.ttd_feeder_before_step(self._feeder)
+        return slot if slot >= 0 else None
 
     def run_step(self) -> None:
         """Enqueue one training step (on the batch fed for it, or on the device-resident data set)."""
-        stream = torch.cuda.current_stream(self.device)
-        slot = self.wait_batch()
-        if self._graph is not None:
-            self._graph.replay()
+        if self._graph_exec is not None:
+            N.check(self.lib.ttd_feeder_step(self._feeder, self._graph_exec, None, None, 0, None, None), "ttd_feeder_step")
         else:
-            self.model.launch_step(sync=self.sync)
-        if slot is not None:
-            self._ev_free[slot].record(stream)
-            self._fed_slot = None
+            self.wait_batch()
+            with torch.cuda.stream(self.stream):
+                self.model.launch_step(sync=self.sync)
+            N.check(self.lib.ttd_feeder_after_step(self._feeder), "ttd_feeder_after_step")
         self._steps_enqueued += 1
+
+    def step_async(self, x, y, fetch: bool = True) -> Optional[int]:
+        """Feed one host batch, run the step and (optionally) start the read-back of its 64-byte state — one
+        native call when the step is a captured graph. Returns the pinned ring slot for ``read_slot``."""
+        if self._graph_exec is None:
+            self.load_batch(x, y)
+            self.run_step()
+            if not fetch:
+                return None
+            with torch.cuda.stream(self.stream):
+                return self.fetch_async()
+        x, y = self._host_batch(x, y)
+        self._host_keep[self._steps_enqueued % 2] = (x, y)
+        slot = self._slot
+        host = self._pinned_state[slot].data_ptr() if fetch else None
+        N.check(self.lib.ttd_feeder_step(self._feeder, self._graph_exec, x.data_ptr(), y.data_ptr(), self._steps_enqueued,
+                                         self.store.state.data_ptr(), host), "ttd_feeder_step")
+        self._steps_enqueued += 1
+        if not fetch:
+            return None
+        self._slot = (slot + 1) % self.RING
+        return slot
 
     def fetch_async(self) -> int:
         """Enqueue a device -> host copy of the step state into the next pinned slot; returns the slot."""
@@ -207,12 +235,9 @@ class GpuTrainer:
 
     def train_step(self, x, y, fetch: bool = True) -> Optional[StepValues]:
         """The user-facing step: feed one batch, run, and (optionally) fetch loss / accuracy / global_step."""
-        with torch.cuda.stream(self.stream):
-            self.load_batch(x, y)
-            self.run_step()
-            if not fetch:
-                return None
-            slot = self.fetch_async()
+        slot = self.step_async(x, y, fetch)
+        if slot is None:
+            return None
         self.stream.synchronize()
         return self.read_slot(slot)
 
@@ -247,3 +272,8 @@ class GpuTrainer:
             self.comm.barrier()
         self._closed = True
         self._graph = None
+        self._graph_exec = None
+        if self._feeder:
+            self.copy_stream.synchronize()
+            self.lib.ttd_feeder_destroy(self._feeder)
+            self._feeder = None

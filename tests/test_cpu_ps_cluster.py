@@ -91,7 +91,9 @@ def test_sync_replicas_two_ps_two_workers(tmp_path):
         assert rc == 0, (k, out[-3000:])
     (s0, g0), (s1, g1) = _final(outs[("worker", 0)][1]), _final(outs[("worker", 1)][1])
     assert g0 >= 120 and g1 >= 120
-    assert 120 <= s0 <= 125 and 120 <= s1 <= 125  # local steps run ~1 ahead of global steps
+    # every global step consumes two gradients; tokens are not bound to a worker, so one replica may run a few
+    # local steps more than the other (same in SyncReplicasOptimizer), but together they cover 2 x 120
+    assert abs(s0 - 120) <= 8 and abs(s1 - 120) <= 8 and s0 + s1 >= 240
     ps0 = outs[("ps", 0)][1]
     m = re.search(r"'applied': (\d+), 'dropped_stale': (\d+)", ps0)
     assert m and int(m.group(1)) >= 120 and int(m.group(2)) >= 1
