@@ -253,7 +253,10 @@ def run(args) -> int:
                 "cuda_graph": cfg.cuda_graph,
             },
             "e2e": {"value": e2e_value, "unit": "examples/s", "ms_per_step": ms_e2e / args.steps,
-                    "h2d_bytes_per_step": B * F * 4 + B * 8, "d2h_bytes_per_step": 64},
+                    "h2d_bytes_per_step": B * F * 4 + B * 8, "d2h_bytes_per_step": 64,
+                    "path": "GpuTrainer.step_async per step: cudaMemcpyAsync of the pinned batch (x fp32 + labels int64) "
+                            "on a copy stream into a 2-slot device pool, graph launch, 64-byte step state written to "
+                            "pinned host memory by the update kernel; separate timed loop from `value`"},
             "gpu_launches": trainer.launches_per_step * args.steps,
             "launches_per_step": trainer.launches_per_step,
             "clocks": sampler.summary(),

@@ -681,6 +681,16 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
       st->metrics_acc[0] = 0.0f;
       st->metrics_acc[1] = 0.0f;
       __threadfence();
+      if (h.host_mirror != nullptr && h.mirror_slots > 0) {
+        // the step's result goes straight into pinned host memory (slot = step index mod ring): no D2H copy
+        // operation sits between this step and the next one on the stream
+        const uint4* src = reinterpret_cast<const uint4*>(st);
+        uint4* dst = reinterpret_cast<uint4*>(static_cast<TtdStepState*>(h.host_mirror) +
+                                              (st->local_step - 1) % static_cast<uint64_t>(h.mirror_slots));
+#pragma unroll
+        for (int i = 0; i < static_cast<int>(sizeof(TtdStepState) / 16); ++i) dst[i] = src[i];
+        __threadfence_system();
+      }
     }
   }
 }

@@ -124,6 +124,10 @@ typedef struct TtdHyper {
   float ema_decay;      /* MOVING_AVERAGE_DECAY (:12); <=0 disables the shadow update */
   int32_t ema_warmup;   /* 1: min(decay, (1+n)/(10+n)) because num_updates=global_step (:156) */
   float grad_scale;     /* multiplies the summed gradient (1/replicas_to_aggregate for the sync mean) */
+  void* host_mirror;    /* pinned host ring of TtdStepState (device-visible address) or NULL: the kernel that ends a
+                           step writes the step's state into slot (local_step - 1) % mirror_slots */
+  int32_t mirror_slots;
+  int32_t reserved;
 } TtdHyper;
 
 /* He / variance-scaling init (reference :49, A.5): truncated normal, sigma = sqrt(1.3*2/fan_in),

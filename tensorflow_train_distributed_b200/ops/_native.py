@@ -69,6 +69,9 @@ class Hyper(C.Structure):
         ("ema_decay", C.c_float),
         ("ema_warmup", C.c_int32),
         ("grad_scale", C.c_float),
+        ("host_mirror", C.c_void_p),
+        ("mirror_slots", C.c_int32),
+        ("reserved", C.c_int32),
     ]
 
 

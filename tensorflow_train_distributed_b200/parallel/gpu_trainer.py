@@ -68,7 +68,10 @@ class GpuTrainer:
                                        pull_fused_first=self.sync and self.world > 1 and cfg.pull_fused and not lenet,
                                        tail_groups=tail)
             self.model = self._build_model()
+            # ring of step states written by the device itself (TtdHyper.host_mirror): slot = step index % RING
             self._pinned_state = torch.zeros(self.RING, 8, dtype=torch.int64).pin_memory()
+            self._pinned_probe = torch.zeros(8, dtype=torch.int64).pin_memory()  # explicit read-backs (slot -1)
+            self.store.set_host_mirror(self._pinned_state.data_ptr(), self.RING)
             # Host-fed batches land in a two-slot device pool; the captured step picks slot local_step % 2 on the
             # device, so the H2D copy of batch s+1 (copy stream) overlaps the compute of batch s (one graph).
             B, F = self.model.x.shape
@@ -83,6 +86,7 @@ class GpuTrainer:
         if not self._feeder:
             raise N.NativeError("ttd_feeder_create failed: " + self.lib.ttd_last_error().decode(errors="replace"))
         self._host_keep = [None, None]
+        self._expect = [0] * self.RING
         self._graph_exec: Optional[int] = None
         self._user_pool = False
         self._graph: Optional[torch.cuda.CUDAGraph] = None
@@ -212,25 +216,28 @@ class GpuTrainer:
                 return self.fetch_async()
         x, y = self._host_batch(x, y)
         self._host_keep[self._steps_enqueued % 2] = (x, y)
-        slot = self._slot
-        host = self._pinned_state[slot].data_ptr() if fetch else None
+        slot = self._steps_enqueued % self.RING  # where the update kernel mirrors this step's state
         N.check(self.lib.ttd_feeder_step(self._feeder, self._graph_exec, x.data_ptr(), y.data_ptr(), self._steps_enqueued,
-                                         self.store.state.data_ptr(), host), "ttd_feeder_step")
+                                         None, None), "ttd_feeder_step")
         self._steps_enqueued += 1
-        if not fetch:
-            return None
-        self._slot = (slot + 1) % self.RING
-        return slot
+        self._expect[slot] = self._steps_enqueued
+        return slot if fetch else None
 
     def fetch_async(self) -> int:
-        """Enqueue a device -> host copy of the step state into the next pinned slot; returns the slot."""
-        slot = self._slot
-        self._pinned_state[slot].copy_(self.store.state, non_blocking=True)
-        self._slot = (slot + 1) % self.RING
-        return slot
+        """Enqueue an explicit device -> host copy of the current step state (slot -1 of ``read_slot``)."""
+        self._pinned_probe.copy_(self.store.state, non_blocking=True)
+        return -1
 
     def read_slot(self, slot: int) -> StepValues:
-        st = N.StepState.from_buffer_copy(self._pinned_state[slot].numpy().tobytes())
+        buf = self._pinned_probe if slot < 0 else self._pinned_state[slot]
+        st = N.StepState.from_buffer_copy(buf.numpy().tobytes())
+        if slot >= 0 and st.local_step != self._expect[slot]:
+            # the device's step counter was advanced behind the trainer's back (a direct store.apply_update):
+            # the mirror slot is not the one predicted, read the state explicitly instead
+            with torch.cuda.stream(self.stream):
+                self.fetch_async()
+            self.stream.synchronize()
+            st = N.StepState.from_buffer_copy(self._pinned_probe.numpy().tobytes())
         return StepValues(st.metrics_out[0], st.metrics_out[1], st.global_step, st.local_step, st.lr_last)
 
     def train_step(self, x, y, fetch: bool = True) -> Optional[StepValues]:

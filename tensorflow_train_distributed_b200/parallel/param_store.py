@@ -171,6 +171,12 @@ class GpuParamStore:
         self._hyper_async = h1.to_native()
 
     # ------------------------------------------------------------------------------------------
+    def set_host_mirror(self, host_ptr: int, slots: int) -> None:
+        """Pinned host ring of 64-byte step states: the kernel that ends a step writes its state there."""
+        for h in (self._hyper_native, self._hyper_async):
+            h.host_mirror = host_ptr
+            h.mirror_slots = slots
+
     def _build_peers(self) -> N.Peers:
         p = N.Peers()
         if self.comm is None:
