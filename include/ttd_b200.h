@@ -248,7 +248,9 @@ int ttd_conv_pool_fwd(const TtdConvDesc* d, const float* x, const void* w, int64
  * bias gradient) into the flat gradient buffer and, if dx != NULL, dx = dL/dx * act_below'(x_act) (fp32, shape of x). */
 int ttd_conv_pool_bwd(const TtdConvDesc* d, const void* dzp, int64_t ld_dzp, int32_t dzp_is_bf16,
                       const uint8_t* argmax, const float* x, const void* w, int64_t ldw, float* dw, float* dx,
-                      const float* x_act, int32_t act_below, void* stream);
+                      const float* x_act, int32_t act_below, float* scratch, int64_t scratch_floats, void* stream);
+/* scratch (optional, NULL: one CTA per kernel row): zero-initialised once by the caller, then owned by this stage;
+ * holds ceil64(K+1) arrival counters followed by slices x (K+1) x 16 partial sums. */
 
 /* cudaMemcpyAsync(device -> device) on `stream`; lets Python snapshot peer-mapped shards for checkpoints. */
 int ttd_copy_d2d(void* dst, const void* src, uint64_t nbytes, void* stream);

@@ -36,6 +36,9 @@ class _ConvStage:
         self.pooled = torch.zeros(B, self.PH, self.PW, cout, device=dev, dtype=torch.float32)
         self.argmax = torch.zeros(B, self.PH, self.PW, cout, device=dev, dtype=torch.uint8)
         self.w = store.w_rm[group]
+        # weight-gradient slices: arrival counters + per-slice partial rows (zeroed once, re-armed by the kernel)
+        k1 = 25 * cin + 1
+        self.wgrad_scratch = torch.zeros(-(-k1 // 64) * 64 + 64 * k1 * 16, device=dev, dtype=torch.float32)
         assert self.w is not None, "conv stages read the TF-layout compute copy (need_w_rm_first=True)"
 
     def forward(self, x: torch.Tensor, flat: Optional[torch.Tensor] = None, flatT: Optional[torch.Tensor] = None) -> None:
@@ -52,7 +55,8 @@ class _ConvStage:
         N.check(lib.ttd_conv_pool_bwd(C.byref(self.desc), dzp.data_ptr(), ld, 1 if dzp.dtype == torch.bfloat16 else 0,
                                       self.argmax.data_ptr(), x.data_ptr(), self.w.data_ptr(), self.w.stride(0),
                                       self.store.grad_matrix(self.group).data_ptr(), N.ptr(dx), x.data_ptr(),
-                                      act_below, N.cur_stream()), "ttd_conv_pool_bwd")
+                                      act_below, self.wgrad_scratch.data_ptr(), self.wgrad_scratch.numel(),
+                                      N.cur_stream()), "ttd_conv_pool_bwd")
         return 2 if dx is not None else 1
 
 

@@ -225,7 +225,8 @@ def load(build_if_missing: bool = True) -> C.CDLL:
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]
     lib.ttd_conv_pool_bwd.restype = C.c_int
     lib.ttd_conv_pool_bwd.argtypes = [C.POINTER(ConvDesc), C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
-                                      C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
+                                      C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+                                      C.c_int64, C.c_void_p]
     lib.ttd_mlp_tail.restype = C.c_int
     lib.ttd_mlp_tail.argtypes = [C.POINTER(TailDesc), C.c_uint64, C.c_uint32, C.c_void_p]
     lib.ttd_copy_d2d.restype = C.c_int
