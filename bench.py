@@ -154,7 +154,7 @@ def run(args) -> int:
     cfg = TrainConfig(job_name="worker", task_id=rank, worker_hosts=hosts, ps_hosts="127.0.0.1:2221",
                       model=spec["model"], sync_replicas=spec["sync_replicas"], batch_size=args.batch,
                       training_steps=10**9, seed=1234, save_checkpoint_secs=None, cuda_graph=not args.no_graph,
-                      pdl=not args.no_pdl, fused_tail=args.fused_tail)
+                      pdl=not args.no_pdl, fused_tail=args.fused_tail, pull_fused=args.pull_fused and not args.no_pull_fused)
     trainer = GpuTrainer(cfg, device_index=local_rank, comm=comm)
     trainer.initialize()
     B, F = cfg.batch_size, cfg.input_dim
@@ -251,6 +251,7 @@ def run(args) -> int:
                 "optimizer": "SGD lr=0.01*0.96^floor(gs/468), L2 0.01, EMA 0.99",
                 "l2_policy": f"inputs larger than L2: {pool_batches * B * F * 4 / 2**20:.0f} MiB device-resident pool rotated per step",
                 "cuda_graph": cfg.cuda_graph,
+                "pull_fused_first_gemm": bool(cfg.pull_fused and cfg.sync_replicas and world > 1 and cfg.model != "lenet"),
             },
             "e2e": {"value": e2e_value, "unit": "examples/s", "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": B * F * 4 + B * 8, "d2h_bytes_per_step": 64,
@@ -282,6 +283,9 @@ def main() -> int:
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-pdl", action="store_true")
     ap.add_argument("--fused-tail", action="store_true", help="run the narrow layers as one chain-kernel launch")
+    ap.add_argument("--pull-fused", action="store_true",
+                    help="fetch W1 from its owners inside the first GEMM (K3) instead of the update kernel's broadcast")
+    ap.add_argument("--no-pull-fused", action="store_true", help="(default) K3 off")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

@@ -96,7 +96,9 @@ class TrainConfig:
     fused_tail: bool = False  # narrow layers behind the first in ONE launch (measured slower than a launch per
     # layer on B200: one CTA serialises epilogues that separate launches spread over several CTAs; see profiles/)
     tail_impl: str = "chain"  # chain: single-CTA tcgen05 chain kernel | cluster: fp32 CUDA-core cluster kernel
-    pull_fused: bool = True  # sync multi-GPU: fetch W1 from its owners inside the first GEMM (K3) instead of broadcasting it
+    pull_fused: bool = False  # sync multi-GPU: fetch W1 from its owners inside the first GEMM (K3) instead of having
+    # the update kernel broadcast it. Measured 2-3 us/step SLOWER on the reference MLP (97.8 vs 95.1 us at 8 GPUs: the
+    # NVLink fetch lands on the forward's critical path, the broadcast hides behind the barrier), hence off by default.
     write_events: bool = True
     inject_fault: str = ""  # "step=N,rank=R" test hook (kill -> resume)
     rendezvous_timeout_secs: float = 120.0

@@ -69,3 +69,14 @@ def test_two_gpu_async_replicas_cli(tmp_path):
     fin = _finals(out)
     assert len(fin) == 2 and all(g >= 400 for _, g in fin)
     assert 400 <= sum(s for s, _ in fin) <= 408  # the global steps are shared (:220-222): ~400 local steps in total
+
+
+@pytest.mark.multigpu
+def test_two_gpu_sync_pull_fused_cli(tmp_path):
+    """K3 (``--pull_fused``): the first GEMM fetches W1 from its owners by TMA instead of K1 broadcasting it."""
+    d = str(tmp_path / "ck")
+    rc, out = _run(2, ["--training_steps=300", "--sync_replicas", "--pull_fused", "--save_checkpoint_secs=none"], d)
+    assert rc == 0, out[-3000:]
+    assert _finals(out) == [(300, 300), (300, 300)]
+    losses = [float(x) for x in re.findall(r"loss on training batch is ([0-9.e+-]+)", out)]
+    assert losses and losses[-1] < 0.5

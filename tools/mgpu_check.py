@@ -99,7 +99,8 @@ def main() -> int:
     model = os.environ.get("CHECK_MODEL", "mlp")
     hosts = ",".join(f"127.0.0.1:{2222 + i}" for i in range(world))
     common = dict(model=model, dropout_rate=0.0, save_checkpoint_secs=None, seed=77, sync_replicas=True,
-                  activation="relu" if model == "wide_mlp" else "elu")
+                  activation="relu" if model == "wide_mlp" else "elu",
+                  pull_fused=os.environ.get("CHECK_PULL_FUSED", "0") == "1")  # K3: W1 fetched inside the first GEMM
     cfg = TrainConfig(worker_hosts=hosts, task_id=rank, batch_size=B, **common)
     tr = GpuTrainer(cfg, device_index=comm.device.index, comm=comm)
     tr.initialize()

@@ -7,5 +7,6 @@ for nv in 1 auto; do
   for m in mlp lenet; do
     TTD_NVLS=$nv CHECK_MODEL=$m run tools/mgpu_check.py 2>&1 | grep "MGPU\|Error\|error" | head -3
   done
+  TTD_NVLS=$nv CHECK_PULL_FUSED=1 run tools/mgpu_check.py 2>&1 | grep "MGPU\|Error\|error" | head -3
   TTD_NVLS=$nv run tools/k1_bench.py 2>&1 | grep "K1BENCH\|Error" | head -3
 done
