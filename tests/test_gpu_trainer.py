@@ -248,3 +248,47 @@ def test_chain_kernel_is_bitwise_the_per_layer_path():
     for k in wa:
         assert np.allclose(wa[k], wb[k], atol=1e-6), k
     a.close(), b.close()
+
+
+def test_loss_curve_tracks_fp32_torch_sgd():
+    """Loss-curve parity (north-star): 150 steps of our bf16 tensor-core pipeline against a plain fp32 PyTorch
+    SGD + L2 + staircase-decay loop started from the same weights and fed the same batches."""
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    cfg = _cfg(dropout_rate=0.0, batch_size=128)
+    tr = GpuTrainer(cfg)
+    tr.initialize()
+    v0 = tr.export_variables()
+    names = [f"hidden{i + 1}" for i in range(len(cfg.layer_sizes) - 1)] + ["output"]
+    ws = [torch.tensor(v0[n + "/kernel"], device="cuda", requires_grad=True) for n in names]
+    bs = [torch.tensor(v0[n + "/bias"], device="cuda", requires_grad=True) for n in names]
+    ds1, ds2 = synthetic_mnist(4096, seed=21), synthetic_mnist(4096, seed=21)
+    ours, ref = [], []
+    for step in range(150):
+        xs, ys = ds1.next_batch(128)
+        ours.append(tr.train_step(xs, ys).loss)
+        xr, yr = ds2.next_batch(128)
+        h = torch.tensor(xr, device="cuda")
+        for i in range(len(names)):
+            h = h @ ws[i] + bs[i]
+            if i < len(names) - 1:
+                h = torch.nn.functional.elu(h)
+        loss = torch.nn.functional.cross_entropy(h, torch.tensor(yr, device="cuda"))
+        ref.append(loss.item())
+        grads = torch.autograd.grad(loss, ws + bs)
+        lr = cfg.initial_learning_rate * cfg.learning_rate_decay_factor ** (step // cfg.decay_steps)
+        with torch.no_grad():
+            for i, w in enumerate(ws):  # L2 on the hidden kernels only (:55 vs :61), none on biases
+                reg = cfg.regularizer_scale * w if i < len(names) - 1 else 0.0
+                w -= lr * (grads[i] + reg)
+            for i, b in enumerate(bs):
+                b -= lr * grads[len(ws) + i]
+    ours, ref = np.array(ours), np.array(ref)
+    assert ref[-1] < 0.5 * ref[0]  # the reference run itself learned
+    assert np.max(np.abs(ours - ref)) < 0.05 * max(1.0, ref[0]), (ours[-5:], ref[-5:])
+    assert abs(ours[-10:].mean() - ref[-10:].mean()) < 0.03
+    vf = tr.export_variables()
+    for i, n in enumerate(names):  # weights stay together too (bf16 operands, fp32 master)
+        d = np.abs(vf[n + "/kernel"] - ws[i].detach().cpu().numpy()).max()
+        assert d < 0.02, (n, d)
+    tr.close()
