@@ -687,8 +687,12 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
         const uint4* src = reinterpret_cast<const uint4*>(st);
         uint4* dst = reinterpret_cast<uint4*>(static_cast<TtdStepState*>(h.host_mirror) +
                                               (st->local_step - 1) % static_cast<uint64_t>(h.mirror_slots));
+        // the chunk holding local_step goes last, behind a fence: a host that polls local_step and sees the new
+        // value also sees the metrics of that step
 #pragma unroll
-        for (int i = 0; i < static_cast<int>(sizeof(TtdStepState) / 16); ++i) dst[i] = src[i];
+        for (int i = 1; i < static_cast<int>(sizeof(TtdStepState) / 16); ++i) dst[i] = src[i];
+        __threadfence_system();
+        dst[0] = src[0];
         __threadfence_system();
       }
     }

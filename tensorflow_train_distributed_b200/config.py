@@ -99,7 +99,12 @@ class TrainConfig:
     pull_fused: bool = False  # sync multi-GPU: fetch W1 from its owners inside the first GEMM (K3) instead of having
     # the update kernel broadcast it. Measured 2-3 us/step SLOWER on the reference MLP (97.8 vs 95.1 us at 8 GPUs: the
     # NVLink fetch lands on the forward's critical path, the broadcast hides behind the barrier), hence off by default.
+    fetch_lag: int = 0  # GPU, graph mode: run() returns the values of step s-L, read from the pinned ring the update
+    # kernel writes, so the host never waits for the step it just enqueued (0 = the reference's exact per-step fetch;
+    # with L > 0 a stop-at-step check sees global_step L steps late, so up to L extra steps run)
     write_events: bool = True
+    metrics_jsonl: bool = True  # every worker: <checkpoint_dir>/metrics-<task>.jsonl, one line per logging period
+    nvtx: bool = False  # NVTX ranges around feed / launch / fetch / checkpoint (Nsight Systems, ncu --nvtx)
     inject_fault: str = ""  # "step=N,rank=R" test hook (kill -> resume)
     rendezvous_timeout_secs: float = 120.0
     stop_grace_period_secs: float = 120.0

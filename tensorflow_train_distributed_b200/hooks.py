@@ -149,6 +149,36 @@ class SummarySaverHook(SessionRunHook):
         self._writer.flush()
 
 
+class MetricsJsonlHook(SessionRunHook):
+    """One JSON line per logging period — ``{"time", "task", "local_step", "global_step", "loss", "accuracy",
+    "steps_per_sec"}`` — in ``<dir>/metrics-<task>.jsonl``. Every worker writes its own file (the events file is
+    the chief's, as with MonitoredTrainingSession's SummarySaverHook); machine-readable twin of the console line
+    (distribute_training.py:232-235)."""
+
+    def __init__(self, path: str, task_id: int = 0, every_n_steps: int = 100):
+        import json as _json
+        self._json = _json
+        os.makedirs(os.path.dirname(path) or ".", exist_ok=True)
+        self._f = open(path, "a", buffering=1)
+        self._task, self._every = task_id, max(1, every_n_steps)
+        self._t_prev: Optional[float] = None
+        self._s_prev = 0
+
+    def after_run(self, ctx, values) -> None:
+        step = ctx.local_step + 1
+        if step % self._every:
+            return
+        now = time.time()
+        rate = (step - self._s_prev) / (now - self._t_prev) if self._t_prev and now > self._t_prev else None
+        self._t_prev, self._s_prev = now, step
+        self._f.write(self._json.dumps({"time": now, "task": self._task, "local_step": step,
+                                        "global_step": int(values.global_step), "loss": float(values.loss),
+                                        "accuracy": float(values.accuracy), "steps_per_sec": rate}) + "\n")
+
+    def end(self, session) -> None:
+        self._f.close()
+
+
 class NanLossHook(SessionRunHook):
     def after_run(self, ctx, values) -> None:
         if values.loss != values.loss:

@@ -18,6 +18,7 @@ from ..config import TrainConfig
 from ..models import mlp as mlp_model
 from ..ops import _native as N
 from .param_store import GpuParamStore, Hyper
+from ..utils.tracing import nvtx_range
 from .sharding import ParamLayout
 
 
@@ -86,6 +87,11 @@ class GpuTrainer:
         if not self._feeder:
             raise N.NativeError("ttd_feeder_create failed: " + self.lib.ttd_last_error().decode(errors="replace"))
         self._host_keep = [None, None]
+        import collections as _collections
+        self._inflight = _collections.deque()
+        self._last_values: Optional[StepValues] = None
+        self._pinned_np = self._pinned_state.numpy()  # host views of the pinned buffers (polled, never copied)
+        self._pinned_np_probe = self._pinned_probe.numpy()
         self._expect = [0] * self.RING
         self._graph_exec: Optional[int] = None
         self._user_pool = False
@@ -141,6 +147,8 @@ class GpuTrainer:
         self._steps_enqueued = 0  # mirrors the device's local_step (which slot of the feed pool a step reads)
         if self.cfg.cuda_graph:
             self._capture()
+        self._inflight.clear()
+        self._last_values = self.read_values()  # global_step of a restored checkpoint, zeros otherwise
         self._initialized = True
 
     def _capture(self) -> None:
@@ -242,16 +250,52 @@ class GpuTrainer:
 
     def train_step(self, x, y, fetch: bool = True) -> Optional[StepValues]:
         """The user-facing step: feed one batch, run, and (optionally) fetch loss / accuracy / global_step."""
-        slot = self.step_async(x, y, fetch)
+        with nvtx_range("ttd.step.enqueue"):
+            slot = self.step_async(x, y, fetch)
         if slot is None:
             return None
-        self.stream.synchronize()
+        lag = self.cfg.fetch_lag if (self._graph_exec is not None and slot >= 0) else 0
+        if lag <= 0:
+            with nvtx_range("ttd.step.fetch"):
+                self.stream.synchronize()
+                return self.read_slot(slot)
+        # pipelined fetch (--fetch_lag L): return the values of step s-L, read from the pinned ring the update
+        # kernel writes — the host never blocks on the step it has just enqueued (M6: no per-step round trip)
+        self._inflight.append(slot)
+        if len(self._inflight) > min(lag, self.RING - 2):
+            self._last_values = self._wait_slot(self._inflight.popleft())
+        return self._last_values  # before the first pipelined step lands: the state laid down by initialize()
+
+    def _wait_slot(self, slot: int, timeout_s: float = 30.0) -> StepValues:
+        """Poll the pinned ring until the device has written step ``_expect[slot]`` (no CUDA call on the way)."""
+        import time as _time
+        want = self._expect[slot]
+        row = self._pinned_np[slot]
+        t0 = None
+        spins = 0
+        while int(row[1]) != want:  # TtdStepState.local_step
+            spins += 1
+            if spins & 0x3FF == 0:
+                now = _time.monotonic()
+                t0 = t0 or now
+                if now - t0 > timeout_s:
+                    break  # fall back to the validated read (synchronises and checks the step counter)
         return self.read_slot(slot)
+
+    def drain(self) -> Optional[StepValues]:
+        """Wait for every pipelined step; returns the values of the last one (None when nothing was in flight)."""
+        last = None
+        while self._inflight:
+            last = self._wait_slot(self._inflight.popleft())
+        if last is not None:
+            self._last_values = last
+        return last
 
     def synchronize(self) -> None:
         self.stream.synchronize()
 
     def read_values(self) -> StepValues:
+        self.drain()
         with torch.cuda.stream(self.stream):
             slot = self.fetch_async()
         self.stream.synchronize()
@@ -262,10 +306,12 @@ class GpuTrainer:
 
     # ---- checkpoint interface --------------------------------------------------------------------
     def export_variables(self) -> Dict[str, np.ndarray]:
-        with torch.cuda.stream(self.stream):
-            self.store.snapshot_owner_shards()  # chief-side peer reads; no collective
-        self.stream.synchronize()
-        return self.store.export_variables()
+        self.drain()
+        with nvtx_range("ttd.checkpoint.export"):
+            with torch.cuda.stream(self.stream):
+                self.store.snapshot_owner_shards()  # chief-side peer reads; no collective
+            self.stream.synchronize()
+            return self.store.export_variables()
 
     def import_variables(self, tensors: Dict[str, np.ndarray]) -> None:
         with torch.cuda.stream(self.stream):

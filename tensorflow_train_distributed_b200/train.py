@@ -81,6 +81,13 @@ def run_worker(cfg: TrainConfig, cluster: cl.ClusterSpec, transport: str) -> int
     if cfg.inject_fault:
         hooks.append(FaultInjectionHook(cfg.inject_fault, task.index))
     check_point_dir = cfg.resolve_checkpoint_dir()  # :204-205
+    if cfg.metrics_jsonl:
+        from .hooks import MetricsJsonlHook
+        hooks.append(MetricsJsonlHook(os.path.join(check_point_dir, f"metrics-{cfg.task_id}.jsonl"), cfg.task_id,
+                                      cfg.log_every_n_steps))
+    if cfg.nvtx:
+        from .utils import tracing
+        tracing.enable_nvtx(True)
 
     reader = PrefetchQueue(dataset, cfg.batch_size, threads=cfg.prefetch) if cfg.prefetch > 0 else None
     step, global_step_value = 0, 0
@@ -103,6 +110,10 @@ def run_worker(cfg: TrainConfig, cluster: cl.ClusterSpec, transport: str) -> int
                 sec_per_batch = duration / max(global_step_value, 1)  # :231 (divides by the GLOBAL step)
                 tlog.log(tlog.format_step(step, global_step_value, v.loss, v.accuracy, sec_per_batch))
             step += 1
+        drain = getattr(trainer, "drain", None)  # --fetch_lag: steps still in flight
+        last = drain() if drain is not None else None
+        if last is not None:
+            global_step_value = last.global_step
     if reader is not None:
         reader.close()
     tlog.log(tlog.format_final(step, global_step_value))  # :238

@@ -292,3 +292,29 @@ def test_loss_curve_tracks_fp32_torch_sgd():
         d = np.abs(vf[n + "/kernel"] - ws[i].detach().cpu().numpy()).max()
         assert d < 0.02, (n, d)
     tr.close()
+
+
+def test_fetch_lag_pipelines_the_readback():
+    """--fetch_lag L: run() hands back step s-L from the pinned ring the update kernel writes; same trajectory."""
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    L = 4
+    a, b = GpuTrainer(_cfg(fetch_lag=0)), GpuTrainer(_cfg(fetch_lag=L))
+    a.initialize(), b.initialize()
+    ds1, ds2 = synthetic_mnist(4096, seed=9), synthetic_mnist(4096, seed=9)
+    exact, lagged = [], []
+    for _ in range(40):
+        exact.append(a.train_step(*ds1.next_batch(128)))
+        lagged.append(b.train_step(*ds2.next_batch(128)))
+    assert [v.local_step for v in exact] == list(range(1, 41))
+    assert all(v.local_step == 0 for v in lagged[:L])          # nothing has landed yet: the initial state
+    for i in range(L, 40):
+        assert lagged[i].local_step == i - L + 1 and lagged[i].global_step == i - L + 1
+        assert abs(lagged[i].loss - exact[i - L].loss) < 1e-6
+    last = b.drain()
+    assert last.local_step == 40 and abs(last.loss - exact[-1].loss) < 1e-6
+    assert b.drain() is None
+    va, vb = a.export_variables(), b.export_variables()
+    for k in va:
+        assert np.allclose(va[k], vb[k], atol=1e-6), k
+    a.close(), b.close()

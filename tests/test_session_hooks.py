@@ -127,3 +127,26 @@ def test_nan_loss_raises():
     with pytest.raises(FloatingPointError):
         with MonitoredTrainingSession(Nan()) as s:
             s.run(None, None)
+
+
+def test_metrics_jsonl_hook_writes_one_line_per_period(tmp_path):
+    import json
+    from tensorflow_train_distributed_b200.hooks import MetricsJsonlHook, SessionRunContext, SessionRunValues
+    path = str(tmp_path / "run" / "metrics-1.jsonl")
+    h = MetricsJsonlHook(path, task_id=1, every_n_steps=10)
+    for step in range(35):
+        h.after_run(SessionRunContext(session=None, local_step=step), SessionRunValues(1.0 / (step + 1), 0.5, 2 * step))
+    h.end(None)
+    rows = [json.loads(line) for line in open(path)]
+    assert [r["local_step"] for r in rows] == [10, 20, 30]
+    assert rows[0]["task"] == 1 and rows[1]["global_step"] == 38 and rows[0]["steps_per_sec"] is None
+    assert rows[2]["steps_per_sec"] > 0
+
+
+def test_nvtx_range_is_a_noop_without_cuda():
+    from tensorflow_train_distributed_b200.utils import tracing
+    tracing.enable_nvtx(True)
+    with tracing.nvtx_range("x"):
+        pass
+    tracing.enable_nvtx(False)
+    assert not tracing.nvtx_enabled()
