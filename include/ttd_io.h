@@ -48,6 +48,19 @@ int ttdio_events_add_scalar(void* writer, const char* tag, float value, int64_t 
 int ttdio_events_flush(void* writer);
 void ttdio_events_close(void* writer);
 
+/* ---- multi-thread batch reader (README.md:5-7 "ReadByQueue"; single-thread form: next_batch, :224) -------- */
+/* Worker threads gather rows of images[n][feat] / labels[n] into a ring of caller-provided batch buffers
+ * (x_slots[i]: batch*feat floats, y_slots[i]: batch int64; pinned host memory on a GPU box). The example order
+ * comes from the caller: batch k = positions [k*batch, (k+1)*batch) of the concatenation of the pushed epoch
+ * permutations (= next_batch's roll-over). Batches come back in order. */
+void* ttdio_loader_create(const float* images, const int64_t* labels, int64_t n, int64_t feat, int32_t batch,
+                          int32_t ring, int32_t threads, float* const* x_slots, int64_t* const* y_slots);
+int ttdio_loader_push_epoch(void* loader, const int64_t* perm, int64_t count);
+int64_t ttdio_loader_backlog(void* loader);              /* pushed stream positions not yet consumed */
+int ttdio_loader_next(void* loader, int32_t timeout_ms); /* ring slot of the next batch; -1 timeout; -2 closed */
+int ttdio_loader_release(void* loader, int64_t upto);    /* batches 0..upto may be overwritten */
+void ttdio_loader_destroy(void* loader);
+
 #ifdef __cplusplus
 }
 #endif

@@ -91,6 +91,7 @@ class TrainConfig:
     data: str = "synthetic"  # synthetic | idx (MNIST idx files under data_path)
     dataset_size: int = 55000  # size of the TF train split
     prefetch: int = 0  # >0: background reader threads (README "ReadByQueue" variant)
+    prefetch_impl: str = "native"  # native: C++ threads filling a pinned ring (csrc/io/loader.cc) | python: queue.Queue
     cuda_graph: bool = True
     pdl: bool = True  # programmatic dependent launch between the kernels of a step
     fused_tail: bool = False  # narrow layers behind the first in ONE launch (measured slower than a launch per

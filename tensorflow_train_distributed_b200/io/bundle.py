@@ -70,6 +70,19 @@ def lib() -> C.CDLL:
         L.ttdio_events_add_scalar.argtypes = [C.c_void_p, C.c_char_p, C.c_float, C.c_int64, C.c_double]
         L.ttdio_events_flush.argtypes = [C.c_void_p]
         L.ttdio_events_close.argtypes = [C.c_void_p]
+        L.ttdio_loader_create.restype = C.c_void_p
+        L.ttdio_loader_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                                          C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.ttdio_loader_push_epoch.restype = C.c_int
+        L.ttdio_loader_push_epoch.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        L.ttdio_loader_backlog.restype = C.c_int64
+        L.ttdio_loader_backlog.argtypes = [C.c_void_p]
+        L.ttdio_loader_next.restype = C.c_int
+        L.ttdio_loader_next.argtypes = [C.c_void_p, C.c_int32]
+        L.ttdio_loader_release.restype = C.c_int
+        L.ttdio_loader_release.argtypes = [C.c_void_p, C.c_int64]
+        L.ttdio_loader_destroy.restype = None
+        L.ttdio_loader_destroy.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 

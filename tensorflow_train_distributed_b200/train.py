@@ -17,7 +17,7 @@ from typing import Optional, Sequence
 
 from . import cluster as cl
 from .config import TrainConfig, parse_flags
-from .data import PrefetchQueue, make_dataset
+from .data import NativePrefetchQueue, PrefetchQueue, make_dataset
 from .hooks import FaultInjectionHook, StopAtStepHook
 from .parallel import sharding
 from .session import MonitoredTrainingSession
@@ -89,7 +89,12 @@ def run_worker(cfg: TrainConfig, cluster: cl.ClusterSpec, transport: str) -> int
         from .utils import tracing
         tracing.enable_nvtx(True)
 
-    reader = PrefetchQueue(dataset, cfg.batch_size, threads=cfg.prefetch) if cfg.prefetch > 0 else None
+    reader = None
+    if cfg.prefetch > 0:  # README.md:5-7 "ReadByQueue": reader threads fill a queue; native (C++) unless asked otherwise
+        if cfg.prefetch_impl == "native":
+            reader = NativePrefetchQueue(dataset, cfg.batch_size, threads=cfg.prefetch, release_lag=cfg.fetch_lag + 3)
+        else:
+            reader = PrefetchQueue(dataset, cfg.batch_size, threads=cfg.prefetch)
     step, global_step_value = 0, 0
     with MonitoredTrainingSession(trainer, is_chief=is_chief, checkpoint_dir=check_point_dir, hooks=hooks,
                                   save_checkpoint_secs=cfg.save_checkpoint_secs,

@@ -62,7 +62,7 @@ def _losses(out):
 def test_async_one_ps_two_workers(tmp_path):
     """The reference's default topology (:26, :29): the 300 global steps are SHARED by the workers (:220-222)."""
     d = str(tmp_path / "ck")
-    outs = _launch(1, 2, ["--training_steps=300", "--save_checkpoint_secs=2"], d)
+    outs = _launch(1, 2, ["--training_steps=300", "--save_checkpoint_secs=2", "--prefetch=2"], d)
     for k, (rc, out) in outs.items():
         assert rc == 0, (k, out[-3000:])
     (s0, g0), (s1, g1) = _final(outs[("worker", 0)][1]), _final(outs[("worker", 1)][1])
