@@ -18,6 +18,8 @@
 #include <string.h>
 
 #include "../include/ttd_b200.h"
+#include <vector>
+
 #include "common.cuh"
 
 namespace ttd {
@@ -993,6 +995,400 @@ extern "C" int ttd_gemm_chain_launch(const void* device_buf, int count, uint64_t
     cfg.numAttrs = 1;
   }
   TTD_CUDA(cudaLaunchKernelEx(&cfg, gemm_chain_kernel, static_cast<const GemmProblem*>(device_buf), h));
+  g_launch_count.fetch_add(1);
+  return 0;
+}
+
+// =====================================================================================================
+// Net kernel: the GEMMs of a whole training step (forward, data gradients, weight gradients) as ONE launch
+// of co-resident CTAs that hand results to each other through global-memory arrival counters.
+//
+// The reference MLP's step is eleven dependent GEMM layers, each one or a few tcgen05 tiles; as separate
+// launches every dependency costs a grid drain + launch (~6.8 us per layer with programmatic dependent launch).
+// Here every tile is a task; a CTA runs its tasks in problem order; before it loads a task's operands it
+// waits (ld.acquire.gpu) until the problems that produce them have counted all their tiles in, and after its
+// epilogue has stored a tile it counts itself in (fence + red.release.gpu). For the reference model there are
+// 114 tiles, i.e. one task per CTA on a 148-SM part: the step becomes a dataflow over SMs, and a dependency
+// costs one L2 round trip instead of a kernel boundary. Deadlock-free because dependencies only point to
+// earlier problems, every CTA visits its tasks in problem order, and the grid never exceeds the SM count
+// (one CTA per SM by shared-memory size), so all CTAs are resident.
+// =====================================================================================================
+namespace ttd {
+
+constexpr int kNetStages = 4;        // smem ring slots, one k-block each
+constexpr int kNetMaxProblems = 24;
+constexpr int kNetBStage = 256 * kBlockK * 2;          // 32 KiB: B k-block at block_n = 256
+constexpr int kNetPatchBytes = 4 * 32 * 36 * 4;        // wgrad epilogue staging (see run_epilogue)
+constexpr int kNetSmemBytes = kNetStages * (kAStageBytes + kNetBStage) + kNetPatchBytes + 1024 + 256;
+
+struct NetHeader {
+  int n_problems;
+  int max_tasks;              // task slots per CTA in `tasks`
+  const int2* tasks;          // [grid][max_tasks] {problem, tile}; problem < 0 ends a CTA's list
+  unsigned int* counters;     // [kNetMaxProblems] tiles finished per problem, [kNetMaxProblems] = CTAs that left
+  const uint32_t* dep_mask;   // [n_problems] bit d: problem d must be complete before this one starts
+  const int* tiles;           // [n_problems] tiles per problem
+  uint32_t seed_lo, seed_hi;
+  const unsigned long long* step_ptr;
+  int use_pdl;
+  unsigned long long* trace;  // optional: per problem (tile 0) {deps met, operands landed, accumulator full, counted in}
+};
+
+__device__ __forceinline__ unsigned int ld_acquire_gpu_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_gpu_add(unsigned int* p, unsigned int v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads, 1) gemm_net_kernel(const GemmProblem* __restrict__ probs, NetHeader h) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + kNetStages * kAStageBytes;
+  uint8_t* patch = sB + kNetStages * kNetBStage;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(patch + kNetPatchBytes);
+  uint64_t* empty_bar = full_bar + kNetStages;
+  uint64_t* acc_full = empty_bar + kNetStages;   // [2] accumulator ready for the epilogue
+  uint64_t* acc_empty = acc_full + 2;            // [2] accumulator drained, MMA may overwrite
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  __shared__ __align__(64) GemmProblem sP[2];    // descriptor of the task whose epilogue is running (per accumulator)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int2* my_tasks = h.tasks + static_cast<long long>(blockIdx.x) * h.max_tasks;
+
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kNetStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&acc_full[a], 1);
+      mbar_init(&acc_empty[a], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 512);  // two 256-column accumulators: the epilogue of task i overlaps the MMAs of task i+1
+    tmem_relinquish();
+  }
+  if (warp == 0 && lane == 0 && my_tasks[0].x >= 0) {
+    tma_prefetch_desc(&probs[my_tasks[0].x].tma_a);
+    tma_prefetch_desc(&probs[my_tasks[0].x].tma_b);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  if (h.use_pdl) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  }
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int j = 0; j < h.max_tasks; ++j) {
+        const int2 t = my_tasks[j];
+        if (t.x < 0) break;
+        const GemmProblem* P = &probs[t.x];
+        const int K = P->K, block_n = P->block_n, tiles_m = P->tiles_m;
+        const int m0 = (t.y % tiles_m) * kBlockM, nbase = (t.y / tiles_m) * block_n;
+        // wait for the producers of this problem's operands
+        uint32_t mask = h.dep_mask[t.x];
+        if (mask != 0) {
+          const uint64_t t0 = globaltimer_ns();
+          while (mask != 0) {
+            const int d = __ffs(mask) - 1;
+            if (ld_acquire_gpu_u32(h.counters + d) >= static_cast<unsigned int>(h.tiles[d])) mask &= mask - 1;
+            else if (globaltimer_ns() - t0 > 4000000000ull) __trap();  // a lost producer raises instead of hanging
+          }
+          // their epilogues stored through the generic proxy; our TMA reads through the async proxy
+          asm volatile("fence.proxy.async.global;" ::: "memory");
+        }
+        if (h.trace != nullptr && t.y == 0) h.trace[4 * t.x + 0] = globaltimer_ns();
+        const int num_kb = (K + kBlockK - 1) / kBlockK;
+        const uint32_t tx = static_cast<uint32_t>(kAStageBytes + block_n * kBlockK * 2);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[s], ph ^ 1u);
+          mbar_arrive_expect_tx(&full_bar[s], tx);
+          tma_load_2d(sA + s * kAStageBytes, &P->tma_a, &full_bar[s], kb * kBlockK, m0);
+          tma_load_2d(sB + s * kNetBStage, &P->tma_b, &full_bar[s], kb * kBlockK, nbase);
+          if (++s == kNetStages) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      uint32_t acc_ph[2] = {0, 0};
+      int acc = 0;
+      for (int j = 0; j < h.max_tasks; ++j) {
+        const int2 t = my_tasks[j];
+        if (t.x < 0) break;
+        const GemmProblem* P = &probs[t.x];
+        const int K = P->K, block_n = P->block_n;
+        const int num_kb = (K + kBlockK - 1) / kBlockK;
+        const uint32_t idesc = umma_idesc_bf16(kBlockM, static_cast<uint32_t>(block_n));
+        mbar_wait(&acc_empty[acc], acc_ph[acc] ^ 1u);  // the epilogue of the task two back has drained it
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc) * 256u;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          if (kb == 0 && h.trace != nullptr && t.y == 0) h.trace[4 * t.x + 1] = globaltimer_ns();
+          const uint32_t a_addr = smem_u32(sA + s * kAStageBytes);
+          const uint32_t b_addr = smem_u32(sB + s * kNetBStage);
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            const uint64_t da = umma_desc_k_sw128(a_addr + k * 32);
+            const uint64_t db = umma_desc_k_sw128(b_addr + k * 32);
+            umma_bf16_ss(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[s]);
+          if (++s == kNetStages) { s = 0; ph ^= 1u; }
+        }
+        umma_commit(&acc_full[acc]);
+        acc_ph[acc] ^= 1u;
+        acc ^= 1;
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue: TMEM -> registers -> global, then count the tile in =====================
+    const EpiCtx E{h.seed_lo, h.seed_hi, h.step_ptr, patch};
+    uint32_t full_ph[2] = {0, 0};
+    int acc = 0;
+    for (int j = 0; j < h.max_tasks; ++j) {
+      const int2 t = my_tasks[j];
+      if (t.x < 0) break;
+      {  // descriptor -> shared memory -> registers (fields read inside the unrolled loops must not be memory operands)
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(&probs[t.x]);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(&sP[acc]);
+        for (int i = threadIdx.x - 128; i < static_cast<int>(sizeof(GemmProblem) / 4); i += 128) dst[i] = src[i];
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      const GemmProblem& S = sP[acc];
+      GemmProblem P;
+      P.M = S.M; P.N = S.N; P.K = S.K; P.block_n = S.block_n; P.tiles_m = S.tiles_m; P.tiles_n = S.tiles_n;
+      P.tile_begin = 0; P.mode = S.mode; P.act = S.act; P.drop_rate = S.drop_rate; P.layer_id = S.layer_id;
+      P.bias = S.bias; P.out = S.out; P.ldo = S.ldo; P.outT = S.outT; P.ldt = S.ldt; P.outf = S.outf;
+      P.ldf = S.ldf; P.aux = S.aux; P.ldaux = S.ldaux; P.scale = S.scale; P.labels = S.labels;
+      P.metrics = S.metrics; P.swap = 0;
+      const int m0 = (t.y % P.tiles_m) * kBlockM, nbase = (t.y / P.tiles_m) * P.block_n;
+      run_epilogue(P, E, tmem_base + static_cast<uint32_t>(acc) * 256u, m0, nbase, warp, lane, &acc_full[acc],
+                   full_ph[acc]);
+      if (h.trace != nullptr && t.y == 0 && threadIdx.x == 128) h.trace[4 * t.x + 2] = globaltimer_ns();
+      tc_fence_before();
+      __threadfence();        // this thread's stores are visible GPU-wide ...
+      fence_proxy_async();    // ... also to other SMs' TMA reads
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (threadIdx.x == 128) {
+        mbar_arrive(&acc_empty[acc]);
+        red_release_gpu_add(h.counters + t.x, 1u);
+        if (h.trace != nullptr && t.y == 0) h.trace[4 * t.x + 3] = globaltimer_ns();
+      }
+      full_ph[acc] ^= 1u;
+      acc ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+  // the last CTA to leave re-arms the counters for the next launch (nobody polls them any more)
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned int left = atomicAdd(h.counters + kNetMaxProblems, 1u);
+    if (left == gridDim.x - 1) {
+      for (int i = 0; i <= kNetMaxProblems; ++i) h.counters[i] = 0;
+      __threadfence();
+    }
+  }
+}
+
+}  // namespace ttd
+
+namespace {
+struct NetLayout {
+  size_t probs, tasks, dep, tiles, counters, total;
+};
+NetLayout net_layout(int count, int grid, int max_tasks) {
+  auto up = [](size_t v) { return (v + 63) & ~size_t(63); };
+  NetLayout L;
+  L.probs = 0;
+  L.tasks = up(static_cast<size_t>(count) * sizeof(ttd::GemmProblem));
+  L.dep = up(L.tasks + static_cast<size_t>(grid) * max_tasks * sizeof(int2));
+  L.tiles = up(L.dep + ttd::kNetMaxProblems * sizeof(uint32_t));
+  L.counters = up(L.tiles + ttd::kNetMaxProblems * sizeof(int));
+  L.total = up(L.counters + (ttd::kNetMaxProblems + 1) * sizeof(unsigned int));
+  return L;
+}
+}  // namespace
+
+extern "C" uint64_t ttd_gemm_net_bytes(int count, int grid, int max_tasks) {
+  return net_layout(count, grid, max_tasks).total;
+}
+
+// Encode `count` problems (dep_mask[i] bit d: problem d < i must be complete first) and a task schedule for
+// `grid` co-resident CTAs into `device_buf` (ttd_gemm_net_bytes bytes, 64-byte aligned, owned by the net from
+// here on). Tile widths are chosen so that, if possible, every tile gets a CTA of its own. Synchronous; set-up only.
+// Returns the number of CTAs to launch (> 0) or a negative error.
+extern "C" int ttd_gemm_net_build(const TtdGemmDesc* d, int count, const uint32_t* dep_mask, int grid, int max_tasks,
+                                  void* device_buf, void* stream) {
+  if (count < 1 || count > kNetMaxProblems || grid < 1 || max_tasks < 1) {
+    set_error("ttd_gemm_net_build: 1..%d problems on >= 1 CTAs, got %d on %d", kNetMaxProblems, count, grid);
+    return -1;
+  }
+  if (reinterpret_cast<uintptr_t>(device_buf) & 63u) {
+    set_error("ttd_gemm_net_build: the buffer must be 64-byte aligned");
+    return -1;
+  }
+  int bn[kNetMaxProblems], tiles_m[kNetMaxProblems], tiles[kNetMaxProblems];
+  for (int i = 0; i < count; ++i) {
+    const TtdGemmDesc& s = d[i];
+    if (s.M < 1 || s.N < 1 || s.K < 1 || s.n_b_peers > 0) {
+      set_error("ttd_gemm_net_build: problem %d: bad shape or peer-fetched operand (not supported here)", i);
+      return -1;
+    }
+    if (dep_mask[i] >> i) {
+      set_error("ttd_gemm_net_build: problem %d may only depend on earlier problems", i);
+      return -1;
+    }
+    if (s.mode == TTD_EPI_FWD_XENT && (s.labels == nullptr || s.N > 256)) {
+      set_error("ttd_gemm_net_build: fused xent needs labels and N <= 256");
+      return -1;
+    }
+    if (s.mode == TTD_EPI_WGRAD && s.outf == nullptr) {
+      set_error("ttd_gemm_net_build: wgrad needs outf");
+      return -1;
+    }
+    const int n16 = ((s.N + 15) / 16) * 16;
+    bn[i] = s.mode == TTD_EPI_FWD_XENT ? n16 : (s.mode == TTD_EPI_WGRAD ? 32 : 16);
+    if (bn[i] > 256) bn[i] = 256;
+    tiles_m[i] = (s.M + kBlockM - 1) / kBlockM;
+  }
+  auto total_tiles = [&]() {
+    int t = 0;
+    for (int i = 0; i < count; ++i) {
+      tiles[i] = tiles_m[i] * ((d[i].N + bn[i] - 1) / bn[i]);
+      t += tiles[i];
+    }
+    return t;
+  };
+  // widen the most fragmented problem until every tile has its own CTA (or nothing can be widened any more)
+  while (total_tiles() > grid) {
+    int worst = -1;
+    for (int i = 0; i < count; ++i)
+      if (d[i].mode != TTD_EPI_FWD_XENT && bn[i] < 256 && bn[i] < ((d[i].N + 15) / 16) * 16 &&
+          (worst < 0 || tiles[i] > tiles[worst]))
+        worst = i;
+    if (worst < 0) break;
+    bn[worst] *= 2;
+  }
+  const int total = total_tiles();
+  if (total > grid * max_tasks) {
+    set_error("ttd_gemm_net_build: %d tiles do not fit %d CTAs x %d tasks", total, grid, max_tasks);
+    return -1;
+  }
+  const int ctas = total < grid ? total : grid;
+  const NetLayout L = net_layout(count, grid, max_tasks);
+  std::vector<uint8_t> host(L.total, 0);
+  GemmProblem* probs = reinterpret_cast<GemmProblem*>(host.data() + L.probs);
+  int2* tasks = reinterpret_cast<int2*>(host.data() + L.tasks);
+  for (int i = 0; i < grid * max_tasks; ++i) tasks[i] = make_int2(-1, 0);
+  int g = 0;
+  for (int i = 0; i < count; ++i) {
+    const TtdGemmDesc& s = d[i];
+    GemmProblem& P = probs[i];
+    int rc = make_tmap(&P.tma_a, s.a, s.M, s.K, s.lda, kBlockM);
+    if (rc) return rc;
+    rc = make_tmap(&P.tma_b, s.b, s.N, s.K, s.ldb, bn[i]);
+    if (rc) return rc;
+    P.M = s.M; P.N = s.N; P.K = s.K;
+    P.block_n = bn[i];
+    P.tiles_m = tiles_m[i];
+    P.tiles_n = (s.N + bn[i] - 1) / bn[i];
+    P.tile_begin = 0;
+    P.mode = s.mode; P.act = s.act; P.drop_rate = s.drop_rate; P.layer_id = s.layer_id;
+    P.bias = s.bias;
+    P.out = static_cast<__nv_bfloat16*>(s.out); P.ldo = s.ldo;
+    P.outT = static_cast<__nv_bfloat16*>(s.outT); P.ldt = s.ldt;
+    P.outf = s.outf; P.ldf = s.ldf;
+    P.aux = static_cast<const __nv_bfloat16*>(s.aux); P.ldaux = s.ldaux;
+    P.scale = s.scale;
+    P.labels = reinterpret_cast<const long long*>(s.labels);
+    P.metrics = s.metrics;
+    P.swap = 0;
+    for (int t = 0; t < tiles[i]; ++t, ++g) tasks[(g % ctas) * max_tasks + g / ctas] = make_int2(i, t);
+  }
+  memcpy(host.data() + L.dep, dep_mask, sizeof(uint32_t) * count);
+  memcpy(host.data() + L.tiles, tiles, sizeof(int) * count);
+  TTD_CUDA(cudaMemcpyAsync(device_buf, host.data(), L.total, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+  TTD_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  return ctas;
+}
+
+static unsigned long long* g_net_trace = nullptr;
+// Diagnostic: device buffer of 4 x n_problems uint64 timestamps (NULL switches it off).
+extern "C" void ttd_gemm_net_set_trace(void* device_buf) { g_net_trace = static_cast<unsigned long long*>(device_buf); }
+
+// `ctas` is what ttd_gemm_net_build returned; grid / max_tasks the values it was built with.
+extern "C" int ttd_gemm_net_launch(const void* device_buf, int count, int grid, int max_tasks, int ctas, uint64_t seed,
+                                   const uint64_t* step_ptr, uint32_t flags, void* stream) {
+  if (count < 1 || count > kNetMaxProblems || ctas < 1 || ctas > grid) {
+    set_error("ttd_gemm_net_launch: bad problem / CTA count (%d, %d of %d)", count, ctas, grid);
+    return -1;
+  }
+  int dev = 0;
+  TTD_CUDA(cudaGetDevice(&dev));
+  static bool attr_set[64] = {false};
+  static int sm_count[64] = {0};
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    TTD_CUDA(cudaFuncSetAttribute(gemm_net_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kNetSmemBytes));
+    TTD_CUDA(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
+    attr_set[dev] = true;
+  }
+  if (dev >= 0 && dev < 64 && ctas > sm_count[dev]) {  // all CTAs must be resident: they wait for one another
+    set_error("ttd_gemm_net_launch: %d CTAs exceed the %d SMs of this device", ctas, sm_count[dev]);
+    return -1;
+  }
+  const NetLayout L = net_layout(count, grid, max_tasks);
+  const uint8_t* base = static_cast<const uint8_t*>(device_buf);
+  NetHeader h;
+  memset(&h, 0, sizeof(h));
+  h.n_problems = count;
+  h.max_tasks = max_tasks;
+  h.tasks = reinterpret_cast<const int2*>(base + L.tasks);
+  h.dep_mask = reinterpret_cast<const uint32_t*>(base + L.dep);
+  h.tiles = reinterpret_cast<const int*>(base + L.tiles);
+  h.counters = reinterpret_cast<unsigned int*>(const_cast<uint8_t*>(base) + L.counters);
+  h.seed_lo = static_cast<uint32_t>(seed);
+  h.seed_hi = static_cast<uint32_t>(seed >> 32);
+  h.step_ptr = reinterpret_cast<const unsigned long long*>(step_ptr);
+  h.use_pdl = (flags & 1u) ? 1 : 0;
+  h.trace = g_net_trace;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(ctas);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kNetSmemBytes;
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  if (h.use_pdl) {
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  TTD_CUDA(cudaLaunchKernelEx(&cfg, gemm_net_kernel, reinterpret_cast<const GemmProblem*>(base + L.probs), h));
   g_launch_count.fetch_add(1);
   return 0;
 }

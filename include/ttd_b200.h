@@ -255,6 +255,17 @@ int ttd_conv_pool_bwd(const TtdConvDesc* d, const void* dzp, int64_t ld_dzp, int
 /* cudaMemcpyAsync(device -> device) on `stream`; lets Python snapshot peer-mapped shards for checkpoints. */
 int ttd_copy_d2d(void* dst, const void* src, uint64_t nbytes, void* stream);
 
+/* ---- net kernel: every GEMM of a step (forward, data and weight gradients) in ONE launch of co-resident CTAs;
+ * a tile is a task, dependent problems hand over through arrival counters in global memory. dep_mask[i] bit d:
+ * problem d (< i) must be complete before problem i starts. The buffer (ttd_gemm_net_bytes, 64-byte aligned)
+ * is encoded once by _build (synchronous; returns the CTA count to launch with, <= grid <= SM count). */
+uint64_t ttd_gemm_net_bytes(int count, int grid, int max_tasks);
+int ttd_gemm_net_build(const TtdGemmDesc* descs, int count, const uint32_t* dep_mask, int grid, int max_tasks,
+                       void* device_buf, void* stream);
+int ttd_gemm_net_launch(const void* device_buf, int count, int grid, int max_tasks, int ctas, uint64_t seed,
+                        const uint64_t* step_ptr, uint32_t flags, void* stream);
+void ttd_gemm_net_set_trace(void* device_buf_4_u64_per_problem);
+
 /* ---- step feeder: the host side of a training step in one native call (reference: the C++ session run loop
  * behind mon_sess.run, distribute_training.py:225). Host batches are copied on `copy_stream` into a two-slot
  * device pool (slot = step & 1; the captured step picks local_step % 2 on the device); events order the copy

@@ -96,7 +96,8 @@ class TrainConfig:
     pdl: bool = True  # programmatic dependent launch between the kernels of a step
     fused_tail: bool = False  # narrow layers behind the first in ONE launch (measured slower than a launch per
     # layer on B200: one CTA serialises epilogues that separate launches spread over several CTAs; see profiles/)
-    tail_impl: str = "chain"  # chain: single-CTA tcgen05 chain kernel | cluster: fp32 CUDA-core cluster kernel
+    tail_impl: str = "chain"  # chain: single-CTA tcgen05 chain kernel | cluster: fp32 CUDA-core cluster kernel |
+    # net: EVERY GEMM of the step in one launch of co-resident CTAs with arrival-counter hand-over (gemm_net_kernel)
     pull_fused: bool = False  # sync multi-GPU: fetch W1 from its owners inside the first GEMM (K3) instead of having
     # the update kernel broadcast it. Measured 2-3 us/step SLOWER on the reference MLP (97.8 vs 95.1 us at 8 GPUs: the
     # NVLink fetch lands on the forward's critical path, the broadcast hides behind the barrier), hence off by default.

@@ -62,7 +62,7 @@ class _ConvStage:
 
 class GpuLeNet:
     def __init__(self, store: GpuParamStore, batch: int, *, activation: str = "elu", dropout_rate: float = 0.01,
-                 seed: int = 0, pdl: bool = False, chain: bool = True):
+                 seed: int = 0, pdl: bool = False, chain: bool = True, net: bool = False):
         self.store, self.B = store, batch
         act = N.ACT_CODES[activation]
         dev = store.device
@@ -70,7 +70,7 @@ class GpuLeNet:
         self.conv1 = _ConvStage(store, 0, batch, 28, 28, 1, 6, True, act)
         self.conv2 = _ConvStage(store, 1, batch, 14, 14, 6, 16, False, act)
         self.head = GpuMlp(store, batch, activation=activation, dropout_rate=dropout_rate, seed=seed, pdl=pdl,
-                           first_group=2, feed_input=False, input_grad=True, chain=chain)
+                           first_group=2, feed_input=False, input_grad=True, chain=chain, net=net)
         self.labels = self.head.labels
         self.dpool1 = torch.zeros(batch, 14, 14, 6, device=dev, dtype=torch.float32)
         self.act = act

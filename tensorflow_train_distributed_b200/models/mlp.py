@@ -54,7 +54,7 @@ def tail_groups(layer_sizes: Sequence[int], batch: int, first_group: int = 0, en
 class GpuMlp:
     def __init__(self, store: GpuParamStore, batch: int, *, activation: str = "elu", dropout_rate: float = 0.01,
                  seed: int = 0, pdl: bool = False, keep_logits: bool = False, first_group: int = 0,
-                 feed_input: bool = True, input_grad: bool = False, chain: bool = True):
+                 feed_input: bool = True, input_grad: bool = False, chain: bool = True, net: bool = False):
         """``first_group`` > 0 makes this the dense head of a larger model (LeNet): its input activations
         ``a[0]`` / ``aT[0]`` are then written by the stage in front (``feed_input=False``) and, with
         ``input_grad``, the backward pass also produces ``dz0`` = dL/d(input) * act'(input) for that stage."""
@@ -89,7 +89,13 @@ class GpuMlp:
         self.use_tail = all((first_group + l) in store.tail_groups for l in range(1, self.L)) and self.L >= 2
         # chain: the narrow layers behind the first run as ONE single-CTA tcgen05 kernel (gemm_chain_kernel)
         self.use_chain = (not self.use_tail) and chain and chain_eligible(sizes, batch)
+        # net: every GEMM of the stack (first layer included) in ONE launch of co-resident CTAs (gemm_net_kernel)
+        self.use_net = bool(net) and not self.use_tail and not (store.pull_fused_first and first_group == 0)
+        if self.use_net:
+            self.use_chain = False
         self._build_descs()
+        if self.use_net:
+            self._build_net()
         if self.use_tail:
             self._build_tail()
         if self.use_chain:
@@ -139,6 +145,25 @@ class GpuMlp:
                 grp.append(gemm.make_desc(self.dz[0], s.w_rm[g0], B, sz[0], sz[1], N.EPI_DGRAD, act=self.act,
                                           drop_rate=0.0, layer_id=0, aux=self.a[0], out=self.dz0))
             self.bwd_descs.append(grp)
+
+    def _build_net(self) -> None:
+        """Problem list + dependencies of the net kernel: F1..FL, then the data gradients DL..D2 (D1 when the stage
+        in front wants one) — the critical path — then the weight gradients WL..W1."""
+        L = self.L
+        descs = list(self.fwd_descs)
+        deps: List[List[int]] = [[] if l == 0 else [l - 1] for l in range(L)]
+        dz_producer = {L: L - 1}  # dz_L comes out of the last forward layer's softmax-xent epilogue
+        for i, grp in enumerate(self.bwd_descs):  # layers L..1
+            if len(grp) > 1:
+                l = L - i
+                descs.append(grp[1])
+                deps.append([dz_producer[l]])
+                dz_producer[l - 1] = len(descs) - 1
+        for i, grp in enumerate(self.bwd_descs):
+            l = L - i
+            descs.append(grp[0])
+            deps.append([dz_producer[l]])
+        self._net = gemm.GemmNet(descs, deps, self.store.device)
 
     # -------------------------------------------------------------------------------------------
     def _build_tail(self) -> None:
@@ -203,6 +228,9 @@ class GpuMlp:
 
     def launch_forward(self) -> int:
         step_ptr, n = self.store.local_step_ptr, 0
+        if self.use_net:  # forward, loss and the whole backward: one launch
+            self._net.launch(seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
+            return 1
         if self.use_tail:  # first layer on the tensor cores, everything behind it in one fused launch
             gemm.gemm_group([self.fwd_descs[0]], seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
             return 1 + self.launch_tail()
@@ -217,6 +245,8 @@ class GpuMlp:
 
     def launch_backward(self) -> int:
         step_ptr, n = self.store.local_step_ptr, 0
+        if self.use_net:
+            return 0
         if self.use_tail or self.use_chain:  # dz of the first layer and every other gradient exist already
             gemm.gemm_group(self.bwd_descs[-1], seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
             return 1

@@ -186,6 +186,16 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.ttd_gemm_chain_build.argtypes = [C.POINTER(GemmDesc), C.c_int, C.c_void_p, C.c_void_p]
     lib.ttd_gemm_chain_launch.restype = C.c_int
     lib.ttd_gemm_chain_launch.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p]
+    lib.ttd_gemm_net_bytes.restype = C.c_uint64
+    lib.ttd_gemm_net_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.ttd_gemm_net_build.restype = C.c_int
+    lib.ttd_gemm_net_build.argtypes = [C.POINTER(GemmDesc), C.c_int, C.POINTER(C.c_uint32), C.c_int, C.c_int, C.c_void_p,
+                                       C.c_void_p]
+    lib.ttd_gemm_net_launch.restype = C.c_int
+    lib.ttd_gemm_net_launch.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_uint32,
+                                        C.c_void_p]
+    lib.ttd_gemm_net_set_trace.restype = None
+    lib.ttd_gemm_net_set_trace.argtypes = [C.c_void_p]
     lib.ttd_softmax_xent.restype = C.c_int
     lib.ttd_softmax_xent.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64,
                                      C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]

@@ -130,3 +130,32 @@ class GemmChain:
         lib = N.load()
         N.check(lib.ttd_gemm_chain_launch(self.ptr, self.n, C.c_uint64(seed & (2**64 - 1)), step_ptr,
                                           1 if pdl else 0, N.cur_stream()), "ttd_gemm_chain_launch")
+
+
+class GemmNet:
+    """All GEMMs of a training step as ONE launch of co-resident CTAs (``gemm_net_kernel``): every tile is a task,
+    dependent problems hand over through arrival counters in global memory instead of kernel boundaries.
+
+    ``deps[i]`` lists the (earlier) problems whose output problem ``i`` reads."""
+
+    MAX_TASKS = 8
+
+    def __init__(self, descs: Sequence[N.GemmDesc], deps: Sequence[Sequence[int]], device: torch.device):
+        lib = N.load()
+        self.n = len(descs)
+        self.grid = torch.cuda.get_device_properties(device).multi_processor_count
+        nbytes = int(lib.ttd_gemm_net_bytes(self.n, self.grid, self.MAX_TASKS))
+        self.buf = torch.zeros(nbytes + 64, dtype=torch.uint8, device=device)
+        self.ptr = (self.buf.data_ptr() + 63) & ~63
+        arr = (N.GemmDesc * self.n)(*descs)
+        masks = (C.c_uint32 * self.n)(*[sum(1 << d for d in dd) for dd in deps])
+        rc = lib.ttd_gemm_net_build(arr, self.n, masks, self.grid, self.MAX_TASKS, self.ptr, N.cur_stream())
+        if rc <= 0:
+            N.check(rc if rc < 0 else -1, "ttd_gemm_net_build")
+        self.ctas = rc
+
+    def launch(self, *, seed: int = 0, step_ptr: Optional[int] = None, pdl: bool = False) -> None:
+        lib = N.load()
+        N.check(lib.ttd_gemm_net_launch(self.ptr, self.n, self.grid, self.MAX_TASKS, self.ctas,
+                                        C.c_uint64(seed & (2**64 - 1)), step_ptr, 1 if pdl else 0, N.cur_stream()),
+                "ttd_gemm_net_launch")

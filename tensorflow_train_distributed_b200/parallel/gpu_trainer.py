@@ -117,11 +117,13 @@ class GpuTrainer:
         if cfg.model in ("mlp", "wide_mlp"):
             return mlp_model.GpuMlp(self.store, cfg.batch_size, activation=cfg.activation,
                                     dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank, pdl=cfg.pdl,
-                                    chain=cfg.fused_tail and cfg.tail_impl == "chain")
+                                    chain=cfg.fused_tail and cfg.tail_impl == "chain",
+                                    net=cfg.fused_tail and cfg.tail_impl == "net")
         from ..models import lenet
         return lenet.GpuLeNet(self.store, cfg.batch_size, activation=cfg.activation,
                               dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank, pdl=cfg.pdl,
-                              chain=cfg.fused_tail and cfg.tail_impl == "chain")
+                              chain=cfg.fused_tail and cfg.tail_impl == "chain",
+                              net=cfg.fused_tail and cfg.tail_impl == "net")
 
     # -------------------------------------------------------------------------------------------
     def initialize(self, restore: Optional[Dict[str, np.ndarray]] = None) -> None:
