@@ -1055,10 +1055,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_net_kernel(const GemmProblem
   uint64_t* acc_empty = acc_full + 2;            // [2] accumulator drained, MMA may overwrite
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   __shared__ __align__(64) GemmProblem sP[2];    // descriptor of the task whose epilogue is running (per accumulator)
+  __shared__ int s_deps_met;                     // tasks of this CTA whose producers have all counted in
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int2* my_tasks = h.tasks + static_cast<long long>(blockIdx.x) * h.max_tasks;
 
   if (warp == 1 && lane == 0) {
+    s_deps_met = 0;
     for (int s = 0; s < kNetStages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -1109,6 +1111,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_net_kernel(const GemmProblem
           // their epilogues stored through the generic proxy; our TMA reads through the async proxy
           asm volatile("fence.proxy.async.global;" ::: "memory");
         }
+        // the epilogue reads producers' results too (saved activations of a data gradient), and prefetches
+        // them before its accumulator is ready: it may not start on task j before this point
+        asm volatile("st.release.cta.shared::cta.s32 [%0], %1;" ::"r"(smem_u32(&s_deps_met)), "r"(j + 1) : "memory");
         if (h.trace != nullptr && t.y == 0) h.trace[4 * t.x + 0] = globaltimer_ns();
         const int num_kb = (K + kBlockK - 1) / kBlockK;
         const uint32_t tx = static_cast<uint32_t>(kAStageBytes + block_n * kBlockK * 2);
@@ -1180,6 +1185,14 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_net_kernel(const GemmProblem
       P.ldf = S.ldf; P.aux = S.aux; P.ldaux = S.ldaux; P.scale = S.scale; P.labels = S.labels;
       P.metrics = S.metrics; P.swap = 0;
       const int m0 = (t.y % P.tiles_m) * kBlockM, nbase = (t.y / P.tiles_m) * P.block_n;
+      {
+        int met;
+        const uint64_t t0 = globaltimer_ns();
+        do {
+          asm volatile("ld.acquire.cta.shared::cta.s32 %0, [%1];" : "=r"(met) : "r"(smem_u32(&s_deps_met)) : "memory");
+          if (met <= j && globaltimer_ns() - t0 > 4000000000ull) __trap();
+        } while (met <= j);
+      }
       run_epilogue(P, E, tmem_base + static_cast<uint32_t>(acc) * 256u, m0, nbase, warp, lane, &acc_full[acc],
                    full_ph[acc]);
       if (h.trace != nullptr && t.y == 0 && threadIdx.x == 128) h.trace[4 * t.x + 2] = globaltimer_ns();

@@ -250,6 +250,26 @@ def test_chain_kernel_is_bitwise_the_per_layer_path():
     a.close(), b.close()
 
 
+def test_net_kernel_is_bitwise_the_per_layer_path():
+    """``--fused_tail --tail_impl net``: every GEMM of the step in ONE launch of co-resident CTAs that hand tiles
+    over through arrival counters. Same pipeline, same epilogues, same Philox streams: identical to the bit."""
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    ds1, ds2 = synthetic_mnist(4096, seed=6), synthetic_mnist(4096, seed=6)
+    a = GpuTrainer(_cfg(dropout_rate=0.1, fused_tail=True, tail_impl="net"))
+    b = GpuTrainer(_cfg(dropout_rate=0.1, fused_tail=False))
+    a.initialize(), b.initialize()
+    assert a.launches_per_step == 3 and b.launches_per_step == 12  # prep + net + update
+    assert a.model._net.ctas == 114  # one CTA per tile for the reference model
+    for _ in range(30):
+        va, vb = a.train_step(*ds1.next_batch(128)), b.train_step(*ds2.next_batch(128))
+    assert abs(va.loss - vb.loss) < 1e-5 and va.global_step == vb.global_step == 30
+    wa, wb = a.export_variables(), b.export_variables()
+    for k in wa:
+        assert np.allclose(wa[k], wb[k], atol=1e-6), k
+    a.close(), b.close()
+
+
 def test_loss_curve_tracks_fp32_torch_sgd():
     """Loss-curve parity (north-star): 150 steps of our bf16 tensor-core pipeline against a plain fp32 PyTorch
     SGD + L2 + staircase-decay loop started from the same weights and fed the same batches."""
