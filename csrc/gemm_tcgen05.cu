@@ -213,7 +213,57 @@ __device__ __forceinline__ void run_epilogue(const GemmProblem& P, const EpiCtx&
   mbar_wait(acc_bar, acc_parity);
   tc_fence_after();
 
-  if (P.mode == TTD_EPI_FWD_XENT) {
+  if (P.mode == TTD_EPI_FWD_XENT && nchunks == 1) {
+    // <= 16 classes (the reference's 10): the whole logit row lives in registers — one TMEM read, the bias and
+    // the label fetched before the accumulator is ready would be better still, but they are L2 hits. Same
+    // operation order as the general path below, hence the same bits.
+    const long long label = row_ok ? P.labels[m] : 0;
+    __syncwarp();
+    tmem_ld16(taddr_row, v);
+    float z[16];
+    float zmax = -INFINITY, zlab = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      z[j] = 0.0f;
+      if (j < P.N) {
+        z[j] = v[j] + (P.bias ? P.bias[j] : 0.0f);
+        zmax = fmaxf(zmax, z[j]);
+        if (j == label) zlab = z[j];
+      }
+    }
+    float sum = 0.0f;
+    int greater = 0;
+    float e[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      e[j] = 0.0f;
+      if (j < P.N) {
+        e[j] = __expf(z[j] - zmax);
+        sum += e[j];
+        greater += (z[j] > zlab) ? 1 : 0;
+      }
+    }
+    const float inv_sum = 1.0f / sum;
+    const float gscale = P.scale / static_cast<float>(P.M);
+    float d[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      d[j] = 0.0f;
+      if (j < P.N) {
+        if (row_ok && P.outf) P.outf[static_cast<long long>(m) * P.ldf + j] = z[j];
+        d[j] = (e[j] * inv_sum - (j == label ? 1.0f : 0.0f)) * gscale;
+      }
+    }
+    if (row_ok) store_row_chunk(P, m, 0, d);
+    float loss = row_ok ? (__logf(sum) + zmax - zlab) / static_cast<float>(P.M) : 0.0f;
+    float corr = (row_ok && greater < 1) ? 1.0f / static_cast<float>(P.M) : 0.0f;
+    loss = warp_sum(loss);
+    corr = warp_sum(corr);
+    if (lane == 0 && P.metrics) {
+      atomicAdd(&P.metrics[0], loss);
+      atomicAdd(&P.metrics[1], corr);
+    }
+  } else if (P.mode == TTD_EPI_FWD_XENT) {
     // One thread owns one example's whole logit row (N <= block_n). Three cheap passes over TMEM.
     const long long label = row_ok ? P.labels[m] : 0;
     float zmax = -INFINITY, zlab = 0.0f;
