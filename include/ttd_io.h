@@ -61,6 +61,26 @@ int ttdio_loader_next(void* loader, int32_t timeout_ms); /* ring slot of the nex
 int ttdio_loader_release(void* loader, int64_t upto);    /* batches 0..upto may be overwritten */
 void ttdio_loader_destroy(void* loader);
 
+/* ---- parameter-server task (--job_name=ps, reference :179-181; in the reference this is TensorFlow's C++ gRPC
+ * worker service). One listening TCP endpoint per ps; request = {op, a, b, c} int64 + optional float32 payload.
+ * Ops: 0 READY, 1 INIT, 2 PULL, 3 PUSH_ASYNC, 4 PUSH_SYNC, 5 TOKEN, 6 GET_STATE, 7 DONE, 8 SYNC_INIT, 9 HELLO
+ * (see csrc/io/ps_server.cc for the payloads and the SyncReplicasOptimizer semantics). */
+typedef struct ttdps_config {
+  int64_t numel;               /* floats in this ps's shard (variables placed round-robin, reference :186-188) */
+  int32_t n_workers, n_agg;    /* workers in the cluster; replicas_to_aggregate (:146) */
+  int32_t tokens_per_step;     /* tokens enqueued per global step: max(total_num_replicas, n_agg) (:147) */
+  int32_t owns_global_step;    /* 1 on the ps that holds global_step (ps 0) */
+  int32_t reg_kind;            /* 0 none, 1 L1, 2 L2 */
+  int32_t use_ema;
+  float reg_scale, ema_decay;
+  double idle_timeout_secs;    /* > 0: serve() returns 1 after this long without a request (once initialised) */
+} ttdps_config;
+void* ttdps_server_create(const char* bind_host, int32_t port, const void* config, const float* reg_mask);
+int32_t ttdps_server_port(void* server);
+int ttdps_server_serve(void* server); /* blocks until every worker sent DONE (0) or the idle limit passed (1) */
+void ttdps_server_stats(void* server, int64_t* out6); /* applied, dropped_stale, pulls, global_step, initialized, done */
+void ttdps_server_destroy(void* server);
+
 #ifdef __cplusplus
 }
 #endif

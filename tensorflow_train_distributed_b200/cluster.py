@@ -85,6 +85,11 @@ def resolve_task(cluster: ClusterSpec, job: str, index: int, transport: str) -> 
         host, port = _split(cluster.task_address("ps", 0))
         rank = index if job == "ps" else n_ps + index
         return TaskInfo(job, index, rank, n_ps + n_w, chief, -1, host, port)
+    if transport == "tcp":  # no process group: every ps listens on its own --ps_hosts entry (:173-177)
+        if n_ps < 1:
+            raise ValueError("the tcp transport needs at least one ps task")
+        host, port = _split(cluster.task_address("ps", 0))
+        return TaskInfo(job, index, index if job == "ps" else n_ps + index, n_ps + n_w, chief, -1, host, port)
     if transport == "nvlink":
         host, port = _split(cluster.task_address("worker", 0))
         if job == "ps":

@@ -85,7 +85,8 @@ class TrainConfig:
     checkpoint_dir: Optional[str] = None  # default: <model_save_path>/run-<utc>-checkpoint (:204-205)
     # ---- new-framework switches ----
     device: str = "auto"  # auto | cuda | cpu
-    transport: str = "auto"  # auto | nvlink (symmetric memory on GPUs) | gloo (real ps processes on CPU)
+    transport: str = "auto"  # auto | nvlink (symmetric memory on GPUs) | gloo (ps processes on CPU, torch.distributed)
+    # | tcp (ps processes on CPU: native C++ server on every --ps_hosts endpoint, csrc/io/ps_server.cc)
     sharding: str = "auto"  # auto | flat | round_robin
     seed: int = 1234
     data: str = "synthetic"  # synthetic | idx (MNIST idx files under data_path)

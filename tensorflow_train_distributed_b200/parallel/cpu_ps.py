@@ -292,8 +292,9 @@ class PsWorkerTrainer:
 
     every_rank_restores = False
 
-    def __init__(self, cfg: TrainConfig, cluster: ClusterSpec, task: TaskInfo, layout: ParamLayout):
+    def __init__(self, cfg: TrainConfig, cluster: ClusterSpec, task: TaskInfo, layout: ParamLayout, channel=None):
         self.cfg, self.cluster, self.task, self.layout = cfg, cluster, task, layout
+        self.chan = channel  # None: gloo send/recv; else an object with call(ps, op, a, b, c, payload, reply_numel)
         self.n_ps = cluster.num_tasks("ps")
         self.place = make_placement(layout, self.n_ps)
         self.specs = {v.name: v for v in self.place.variables}
@@ -310,6 +311,8 @@ class PsWorkerTrainer:
 
     # -- rpc helpers ---------------------------------------------------------------------------------------
     def _call(self, ps: int, op: int, a: int = 0, b: int = 0, c: int = 0, payload=None, reply_numel: int = 0):
+        if self.chan is not None:
+            return self.chan.call(ps, op, a, b, c, payload, reply_numel)
         try:
             _send(ps, op, a, b, c, payload)
             hdr = torch.zeros(4, dtype=torch.int64)
@@ -418,3 +421,5 @@ class PsWorkerTrainer:
                 self._call(k, OP_DONE)
             except TransportError:
                 pass
+        if self.chan is not None:
+            self.chan.close()

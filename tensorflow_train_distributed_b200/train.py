@@ -41,6 +41,13 @@ def run_ps(cfg: TrainConfig, cluster: cl.ClusterSpec, transport: str) -> int:
         tlog.log(f"ps {cfg.task_id} done: {stats}")
         dist.destroy_process_group()
         return 0
+    if transport == "tcp":
+        from .parallel.tcp_ps import NativePsServer
+        server = NativePsServer(cfg, cluster, task, build_layout(cfg))
+        stats = server.serve()
+        server.close()
+        tlog.log(f"ps {cfg.task_id} done: {stats}")
+        return 0
     # nvlink: the parameter store is GPU memory owned by the workers; a ps process only keeps the CLI contract
     tlog.log(f"ps {cfg.task_id}: parameters live in the workers' GPU memory (nvlink transport); nothing to serve")
     return 0
@@ -57,6 +64,12 @@ def run_worker(cfg: TrainConfig, cluster: cl.ClusterSpec, transport: str) -> int
         from .parallel.cpu_ps import PsWorkerTrainer, init_gloo
         init_gloo(task, cfg.rendezvous_timeout_secs)
         trainer = PsWorkerTrainer(cfg, cluster, task, layout)
+        n_shards = cluster.num_tasks("ps")
+    elif transport == "tcp":
+        from .parallel.cpu_ps import PsWorkerTrainer
+        from .parallel.tcp_ps import TcpChannel
+        trainer = PsWorkerTrainer(cfg, cluster, task, layout,
+                                  channel=TcpChannel(cluster, task.index, cfg.rendezvous_timeout_secs))
         n_shards = cluster.num_tasks("ps")
     else:
         import torch

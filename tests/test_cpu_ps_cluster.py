@@ -59,10 +59,11 @@ def _losses(out):
 
 
 @pytest.mark.timeout(300)
-def test_async_one_ps_two_workers(tmp_path):
+@pytest.mark.parametrize("transport", ["gloo", "tcp"])
+def test_async_one_ps_two_workers(tmp_path, transport):
     """The reference's default topology (:26, :29): the 300 global steps are SHARED by the workers (:220-222)."""
     d = str(tmp_path / "ck")
-    outs = _launch(1, 2, ["--training_steps=300", "--save_checkpoint_secs=2", "--prefetch=2"], d)
+    outs = _launch(1, 2, ["--training_steps=300", "--save_checkpoint_secs=2", "--prefetch=2", f"--transport={transport}"], d)
     for k, (rc, out) in outs.items():
         assert rc == 0, (k, out[-3000:])
     (s0, g0), (s1, g1) = _final(outs[("worker", 0)][1]), _final(outs[("worker", 1)][1])
@@ -81,12 +82,13 @@ def test_async_one_ps_two_workers(tmp_path):
 
 
 @pytest.mark.timeout(300)
-def test_sync_replicas_two_ps_two_workers(tmp_path):
+@pytest.mark.parametrize("transport", ["gloo", "tcp"])
+def test_sync_replicas_two_ps_two_workers(tmp_path, transport):
     """SyncReplicasOptimizer semantics (A.2): every worker runs ~last_step local steps, one global step per
     aggregate, stale second gradient dropped, variables spread round-robin over two ps tasks."""
     d = str(tmp_path / "ck")
     outs = _launch(2, 2, ["--training_steps=120", "--sync_replicas", "--save_checkpoint_secs=none",
-                          "--save_checkpoint_steps=60", "--dropout_rate=0"], d)
+                          "--save_checkpoint_steps=60", "--dropout_rate=0", f"--transport={transport}"], d)
     for k, (rc, out) in outs.items():
         assert rc == 0, (k, out[-3000:])
     (s0, g0), (s1, g1) = _final(outs[("worker", 0)][1]), _final(outs[("worker", 1)][1])
@@ -103,10 +105,11 @@ def test_sync_replicas_two_ps_two_workers(tmp_path):
 
 
 @pytest.mark.timeout(400)
-def test_kill_and_resume_from_checkpoint(tmp_path):
+@pytest.mark.parametrize("transport", ["gloo", "tcp"])
+def test_kill_and_resume_from_checkpoint(tmp_path, transport):
     """--inject_fault kills the chief mid-run; a relaunch on the same --checkpoint_dir resumes (:208)."""
     d = str(tmp_path / "ck")
-    common = ["--training_steps=200", "--save_checkpoint_secs=none", "--save_checkpoint_steps=40"]
+    common = ["--training_steps=200", "--save_checkpoint_secs=none", "--save_checkpoint_steps=40", f"--transport={transport}"]
     outs = _launch(1, 1, common + ["--inject_fault=step=90,rank=0", "--ps_idle_timeout_secs=3"], d, timeout=120)
     assert "idle_timeout" in outs[("ps", 0)][1]  # the ps noticed that its only worker is gone
     assert outs[("worker", 0)][0] != 0  # killed
@@ -118,3 +121,33 @@ def test_kill_and_resume_from_checkpoint(tmp_path):
     assert rc == 0, out[-3000:]
     steps, gs = _final(out)
     assert gs >= 200 and steps <= 200 - mid + 2  # only the remaining steps were run
+
+
+@pytest.mark.timeout(300)
+def test_native_ps_survives_a_worker_restart(tmp_path):
+    """tcp transport: the ps is a listening server that keeps its state when its worker dies; the restarted
+    chief reconnects, restores the last checkpoint into the live ps and finishes (the recovery the reference
+    gets from MonitoredTrainingSession + a long-lived tf.train.Server, :175-181, :208)."""
+    d = str(tmp_path / "ck")
+    ports = _free_ports(2)
+    base = [sys.executable, "-m", "tensorflow_train_distributed_b200.train", f"--ps_hosts=127.0.0.1:{ports[0]}",
+            f"--worker_hosts=127.0.0.1:{ports[1]}", "--device=cpu", "--dataset_size=4096", f"--checkpoint_dir={d}",
+            "--log_every_n_steps=50", "--transport=tcp", "--training_steps=200", "--save_checkpoint_secs=none",
+            "--save_checkpoint_steps=40"]
+    env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="1", MKL_NUM_THREADS="1")
+    ps = subprocess.Popen(base + ["--job_name=ps", "--task_id=0"], env=env, cwd=ROOT, stdout=subprocess.PIPE,
+                          stderr=subprocess.STDOUT, text=True)
+    try:
+        w1 = subprocess.run(base + ["--job_name=worker", "--task_id=0", "--inject_fault=step=90,rank=0"], env=env,
+                            cwd=ROOT, capture_output=True, text=True, timeout=120)
+        assert w1.returncode != 0 and ps.poll() is None  # the worker was killed, the ps is still serving
+        w2 = subprocess.run(base + ["--job_name=worker", "--task_id=0"], env=env, cwd=ROOT, capture_output=True,
+                            text=True, timeout=120)
+        assert w2.returncode == 0, (w2.stdout + w2.stderr)[-3000:]
+        steps, gs = _final(w2.stdout + w2.stderr)
+        assert gs >= 200 and steps <= 200 - 40 + 2  # resumed from a checkpoint at step >= 40
+        out, _ = ps.communicate(timeout=30)
+        assert ps.returncode == 0 and "ps 0 done" in out
+    finally:
+        if ps.poll() is None:
+            ps.kill()
