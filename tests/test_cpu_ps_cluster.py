@@ -95,7 +95,11 @@ def test_sync_replicas_two_ps_two_workers(tmp_path, transport):
     assert g0 >= 120 and g1 >= 120
     # every global step consumes two gradients; tokens are not bound to a worker, so one replica may run a few
     # local steps more than the other (same in SyncReplicasOptimizer), but together they cover 2 x 120
-    assert abs(s0 - 120) <= 8 and abs(s1 - 120) <= 8 and s0 + s1 >= 240
+    assert s0 + s1 >= 240
+    if transport == "gloo":  # the process-group rendezvous starts both workers together: near lock-step
+        assert abs(s0 - 120) <= 8 and abs(s1 - 120) <= 8
+    # tcp: as with TF, nothing makes a worker wait for its peers — tokens are not bound to a worker, so one that
+    # starts earlier can contribute both gradients of an aggregate until the other has connected
     ps0 = outs[("ps", 0)][1]
     m = re.search(r"'applied': (\d+), 'dropped_stale': (\d+)", ps0)
     assert m and int(m.group(1)) >= 120 and int(m.group(2)) >= 1
