@@ -73,7 +73,21 @@ class CpuMlp:
         h = x
         groups = self.layout.groups
         for i, g in enumerate(groups):
-            h = h @ leaves[g.kernel_name] + leaves[g.bias_name]
+            k = leaves[g.kernel_name]
+            if k.dim() == 4:  # LeNet conv stage (config 5): HWIO kernel, SAME padding for the first, 2x2 max-pool
+                kh, kw, cin, cout = k.shape
+                if h.dim() == 2:
+                    side = int(round((h.shape[1] // cin) ** 0.5))
+                    h = h.view(-1, side, side, cin).permute(0, 3, 1, 2)  # NHWC batch -> NCHW
+                h = torch.nn.functional.conv2d(h, k.permute(3, 2, 0, 1), leaves[g.bias_name],
+                                               padding=(kh // 2) if i == 0 else 0)
+                h = torch.nn.functional.elu(h) if self.activation == "elu" else (
+                    torch.relu(h) if self.activation == "relu" else h)
+                h = torch.nn.functional.max_pool2d(h, 2)
+                continue
+            if h.dim() == 4:
+                h = h.permute(0, 2, 3, 1).reshape(h.shape[0], -1)  # TF flatten order [H, W, C]
+            h = h @ k + leaves[g.bias_name]
             if i < len(groups) - 1:
                 if self.activation == "elu":
                     h = torch.nn.functional.elu(h)
@@ -87,7 +101,7 @@ class CpuMlp:
         loss.backward()
         zl = h.gather(1, y.view(-1, 1))
         acc = ((h > zl).sum(1) < 1).float().mean()  # in_top_k(logits, labels, 1)
-        return float(loss), float(acc), {k: v.grad for k, v in leaves.items()}
+        return float(loss.detach()), float(acc), {k: v.grad for k, v in leaves.items()}
 
 
 def he_init(layout: ParamLayout, seed: int) -> Dict[str, np.ndarray]:

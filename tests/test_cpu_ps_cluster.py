@@ -155,3 +155,24 @@ def test_native_ps_survives_a_worker_restart(tmp_path):
     finally:
         if ps.poll() is None:
             ps.kill()
+
+
+def test_cpu_worker_model_covers_lenet():
+    """Config 5 on the CPU tier: the worker-side model handles the LeNet layout (HWIO conv kernels, SAME conv1,
+    TF flatten order) and its gradients have the variables' shapes."""
+    import torch
+    from tensorflow_train_distributed_b200.parallel import sharding
+    from tensorflow_train_distributed_b200.parallel.cpu_ps import CpuMlp, he_init
+    lay = sharding.ParamLayout(sharding.lenet_groups(10))
+    p = {k: torch.from_numpy(v) for k, v in he_init(lay, 1).items()}
+    assert sum(v.numel() for v in p.values()) == 61706
+    m = CpuMlp(lay, "elu", 0.0, 3)
+    g = torch.Generator().manual_seed(0)
+    x, y = torch.rand(32, 784, generator=g), torch.randint(0, 10, (32,), generator=g)
+    first = None
+    for _ in range(40):
+        loss, acc, grads = m.loss_and_grads(p, x, y)
+        first = first or loss
+        assert all(grads[k].shape == p[k].shape for k in p)
+        p = {k: p[k] - 0.05 * grads[k] for k in p}
+    assert loss < 0.3 * first and acc > 0.9
