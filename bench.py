@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Headline benchmark: examples/sec of the reference training step on N B200 GPUs of one node.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference|ddp] [--config mnist_sync|...]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference|ddp|zero1|torch_graph] [--config mnist_sync|...]
 
 Metric and config are BASELINE.json's: the distribute_training.py model (784-200-100-50-25-10 ELU MLP, dropout
 0.01, batch 128 per worker, SGD with staircase-decayed lr), synchronous replicas on a GPU-sharded parameter
@@ -139,6 +139,12 @@ def run(args) -> int:
     if args.impl == "ddp":
         from baseline.ddp_mlp import run_ddp_bench
         return run_ddp_bench(args, rank, world, local_rank)
+    if args.impl == "zero1":
+        from baseline.zero1_mlp import run_zero1_bench
+        return run_zero1_bench(args, rank, world, local_rank)
+    if args.impl == "torch_graph":
+        from baseline.zero1_mlp import run_torch_graph_bench
+        return run_torch_graph_bench(args, rank, world, local_rank)
 
     from tensorflow_train_distributed_b200.config import TrainConfig
     from tensorflow_train_distributed_b200.data import synthetic_mnist
@@ -277,7 +283,7 @@ def main() -> int:
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=50)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "ddp"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "ddp", "zero1", "torch_graph"])
     ap.add_argument("--config", default="mnist_sync", choices=sorted(CONFIGS))
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--no-graph", action="store_true")
