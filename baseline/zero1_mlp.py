@@ -177,7 +177,9 @@ def run_torch_graph_bench(args, rank, world, local_rank) -> int:
             torch._foreach_sub_(params, upd)
             n_t.add_(1)
             d = torch.minimum(torch.full_like(n_t, 0.99), (1 + n_t) / (10 + n_t))
-            torch._foreach_lerp_(ema, params, 1 - d)
+            w = 1 - d
+            for e, p in zip(ema, params):  # tensor weight: no host read-back inside the capture
+                e.lerp_(p, w)
             lr_t.copy_(0.01 * torch.pow(torch.full_like(n_t, 0.96), torch.floor(n_t / 468)))
             loss_out.copy_(loss.detach())
 
