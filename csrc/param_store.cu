@@ -687,13 +687,20 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
         const uint4* src = reinterpret_cast<const uint4*>(st);
         uint4* dst = reinterpret_cast<uint4*>(static_cast<TtdStepState*>(h.host_mirror) +
                                               (st->local_step - 1) % static_cast<uint64_t>(h.mirror_slots));
-        // the chunk holding local_step goes last, behind a fence: a host that polls local_step and sees the new
-        // value also sees the metrics of that step
-#pragma unroll
-        for (int i = 1; i < static_cast<int>(sizeof(TtdStepState) / 16); ++i) dst[i] = src[i];
-        __threadfence_system();
+        // No fence between the four 16-byte stores (a system fence costs a PCIe round trip on the step's critical
+        // path): the copy carries the low word of local_step as a tag in every chunk (in place of fields the host
+        // does not read: metrics_acc[0], done_counter, reserved[5]), so a host that POLLS the slot accepts it
+        // only once all four chunks of this step have landed; a host that synchronises the stream first sees
+        // them all anyway.
+        const uint32_t tag = static_cast<uint32_t>(st->local_step);
+        uint4 c1 = src[1], c2 = src[2], c3 = src[3];
+        c1.x = tag;
+        c2.x = tag;
+        c3.w = tag;
+        dst[1] = c1;
+        dst[2] = c2;
+        dst[3] = c3;
         dst[0] = src[0];
-        __threadfence_system();
       }
     }
   }

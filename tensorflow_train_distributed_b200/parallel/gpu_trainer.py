@@ -91,6 +91,7 @@ class GpuTrainer:
         self._inflight = _collections.deque()
         self._last_values: Optional[StepValues] = None
         self._pinned_np = self._pinned_state.numpy()  # host views of the pinned buffers (polled, never copied)
+        self._pinned_u32 = self._pinned_np.view(np.uint32)
         self._pinned_np_probe = self._pinned_probe.numpy()
         self._expect = [0] * self.RING
         self._graph_exec: Optional[int] = None
@@ -147,6 +148,7 @@ class GpuTrainer:
                 self.comm.reset_flags(self.store)
                 self.comm.barrier()
         self._steps_enqueued = 0  # mirrors the device's local_step (which slot of the feed pool a step reads)
+        self._pinned_state.zero_()  # entries of the warm-up step (or of an earlier run) must not pass for new ones
         if self.cfg.cuda_graph:
             self._capture()
         self._inflight.clear()
@@ -272,10 +274,12 @@ class GpuTrainer:
         """Poll the pinned ring until the device has written step ``_expect[slot]`` (no CUDA call on the way)."""
         import time as _time
         want = self._expect[slot]
-        row = self._pinned_np[slot]
+        row = self._pinned_u32[slot]  # 16 words: local_step = [2:4]; per-chunk tags (low word of local_step) at 4, 8, 15
+        tag = want & 0xFFFFFFFF
         t0 = None
         spins = 0
-        while int(row[1]) != want:  # TtdStepState.local_step
+        while not (int(row[2]) == tag and int(row[3]) == (want >> 32) and int(row[4]) == tag and int(row[8]) == tag
+                   and int(row[15]) == tag):  # every 16-byte chunk of this step has landed
             spins += 1
             if spins & 0x3FF == 0:
                 now = _time.monotonic()
