@@ -9,7 +9,6 @@ from __future__ import annotations
 
 import json
 import os
-import time
 
 import torch
 import torch.distributed as dist

@@ -7,7 +7,7 @@ the reference's variable names, with tensor *k*'s bytes in the shard of the ps t
 from __future__ import annotations
 
 import ctypes as C
-from typing import Dict, Iterable, List, Mapping, Optional, Tuple
+from typing import Dict, List, Mapping, Optional
 
 import numpy as np
 

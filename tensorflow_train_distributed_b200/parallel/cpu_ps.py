@@ -21,13 +21,13 @@ import collections
 import datetime as _dt
 import time
 from dataclasses import dataclass
-from typing import Dict, List, Optional, Tuple
+from typing import Dict, List, Optional
 
 import numpy as np
 import torch
 import torch.distributed as dist
 
-from ..cluster import ClusterSpec, TaskInfo, resolve_task
+from ..cluster import ClusterSpec, TaskInfo
 from ..config import TrainConfig
 from ..session import TransportError
 from ..utils.schedule import ema_decay, exponential_decay

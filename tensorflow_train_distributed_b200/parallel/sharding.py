@@ -17,8 +17,8 @@ Two plans are provided:
 """
 from __future__ import annotations
 
-from dataclasses import dataclass, field
-from typing import Dict, List, Optional, Sequence, Tuple
+from dataclasses import dataclass
+from typing import Dict, List, Sequence, Tuple
 
 GLOBAL_STEP = "global_step"
 EMA_SUFFIX = "/ExponentialMovingAverage"

@@ -17,7 +17,7 @@ import torch
 from ..cluster import ClusterSpec, TaskInfo
 from ..config import TrainConfig
 from ..session import TransportError
-from .cpu_ps import OP_DONE, make_placement
+from .cpu_ps import make_placement
 from .sharding import GLOBAL_STEP, ParamLayout
 
 OP_HELLO = 9
