@@ -176,3 +176,21 @@ def test_cpu_worker_model_covers_lenet():
         assert all(grads[k].shape == p[k].shape for k in p)
         p = {k: p[k] - 0.05 * grads[k] for k in p}
     assert loss < 0.3 * first and acc > 0.9
+
+
+@pytest.mark.timeout(300)
+def test_cluster_launcher_spawns_every_task(tmp_path):
+    """``python -m ...launch``: one subprocess per ps / worker task of the ClusterSpec, prefixed output, exit code."""
+    ports = _free_ports(3)
+    cmd = [sys.executable, "-m", "tensorflow_train_distributed_b200.launch", f"--ps_hosts=127.0.0.1:{ports[0]}",
+           f"--worker_hosts=127.0.0.1:{ports[1]},127.0.0.1:{ports[2]}", "--device=cpu", "--transport=tcp",
+           "--dataset_size=2048", "--training_steps=80", "--save_checkpoint_secs=none", "--log_every_n_steps=20",
+           f"--checkpoint_dir={tmp_path / 'ck'}"]
+    env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="1", MKL_NUM_THREADS="1")
+    r = subprocess.run(cmd, env=env, cwd=ROOT, capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
+    out = r.stdout
+    assert "[ps:0] " in out and "[worker:0] " in out and "[worker:1] " in out
+    finals = re.findall(r"\[worker:(\d)\] .*total step: (\d+), global_step: (\d+)", out)
+    assert len(finals) == 2 and all(int(g) >= 80 for _, _, g in finals)
+    assert "ps 0 done" in out
