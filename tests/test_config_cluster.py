@@ -61,8 +61,8 @@ def test_cluster_spec_and_rank_maps():
     assert cl.worker_ranks(c) == [2, 3, 4] and cl.ps_ranks(c) == [0, 1]
     with pytest.raises(ValueError):
         cl.ClusterSpec({"ps": ["nohostport"]})
-    assert cl.choose_transport(TrainConfig(device="cpu"), True) == "gloo"
-    assert cl.choose_transport(TrainConfig(), True) == "nvlink" and cl.choose_transport(TrainConfig(), False) == "gloo"
+    assert cl.choose_transport(TrainConfig(device="cpu"), True) == "tcp"
+    assert cl.choose_transport(TrainConfig(), True) == "nvlink" and cl.choose_transport(TrainConfig(), False) == "tcp"
 
 
 def test_variable_catalogue_and_round_robin():
