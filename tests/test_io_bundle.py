@@ -181,3 +181,29 @@ def test_events_writer_roundtrip(tmp_path):
     assert evs[0]["file_version"] == "brain.Event:2"
     assert evs[1]["step"] == 100 and evs[1]["wall_time"] == 12.5 and evs[1]["scalars"] == {"loss_0": 0.5}
     assert evs[2]["scalars"] == {"accuracy_0": 0.875} and evs[3]["scalars"] == {"global_step/sec": 2500.0}
+
+
+def test_inspect_cli_lists_and_exports_a_torch_state_dict(tmp_path, capsys):
+    import torch
+    from tensorflow_train_distributed_b200.io import checkpoint, inspect as insp
+    rng = np.random.default_rng(0)
+    tensors = {"global_step": np.asarray(7, dtype=np.int64),
+               "hidden1/kernel": rng.standard_normal((784, 200)).astype(np.float32), "hidden1/bias": np.zeros(200, np.float32),
+               "conv1/kernel": rng.standard_normal((5, 5, 1, 6)).astype(np.float32), "conv1/bias": np.ones(6, np.float32),
+               "hidden1/kernel/ExponentialMovingAverage": np.full((784, 200), 0.5, np.float32)}
+    saver = checkpoint.Saver(str(tmp_path))
+    saver.save(tensors, 7)
+    out_file = str(tmp_path / "sd.pt")
+    assert insp.main([str(tmp_path), "--tensor", "conv1/bias", "--to_torch", out_file]) == 0
+    text = capsys.readouterr().out
+    assert "6 tensors in 1 data shard" in text and "hidden1/kernel" in text and "(784, 200)" in text
+    assert "conv1/bias = [1. 1. 1. 1. 1. 1.]" in text
+    sd = torch.load(out_file)
+    assert sd["hidden1.weight"].shape == (200, 784) and int(sd["global_step"]) == 7
+    x = torch.randn(3, 784)
+    assert torch.allclose(torch.nn.functional.linear(x, sd["hidden1.weight"], sd["hidden1.bias"]),
+                          x @ torch.from_numpy(tensors["hidden1/kernel"]), atol=1e-3, rtol=1e-4)
+    assert sd["conv1.weight"].shape == (6, 1, 5, 5)
+    assert torch.equal(sd["conv1.weight"][2, 0], torch.from_numpy(tensors["conv1/kernel"][:, :, 0, 2]))
+    ema = insp.to_torch_state_dict(insp.resolve_prefix(str(tmp_path)), ema=True)
+    assert float(ema["hidden1.weight"].mean()) == 0.5
