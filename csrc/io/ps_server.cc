@@ -105,8 +105,8 @@ struct Server {
   std::chrono::steady_clock::time_point last_msg;
   bool stopping = false;
 
-  std::vector<std::thread> conn_threads;
-  std::vector<int> conn_fds;
+  std::vector<int> conn_fds;  // open connections (their threads are detached and counted in active_conns)
+  int active_conns = 0;
 
   void apply(const float* grad, float scale, double lr, int64_t gs_after) {
     const int64_t n = cfg.numel;
@@ -176,7 +176,7 @@ struct Server {
           std::lock_guard<std::mutex> lk(mu);
           touch();
           if (cfg.owns_global_step)
-            for (int64_t i = 0; i < a; ++i) tokens.push_back(global_step);
+            for (int64_t i = 0; i < a && i < 4096; ++i) tokens.push_back(global_step);
         }
         cv.notify_all();
         reply[1] = 1;
@@ -288,12 +288,13 @@ struct Server {
     std::vector<float> scratch;
     while (handle(fd, &worker_id, &scratch)) {
     }
+    ::close(fd);
     {
       std::lock_guard<std::mutex> lk(mu);
       conn_fds.erase(std::remove(conn_fds.begin(), conn_fds.end(), fd), conn_fds.end());
+      --active_conns;  // last touch of the server by this thread: destroy() may free it once this reaches zero
+      cv.notify_all();
     }
-    ::close(fd);
-    cv.notify_all();
   }
 };
 
@@ -380,7 +381,8 @@ int ttdps_server_serve(void* h) {
       if (cfd >= 0) {
         std::lock_guard<std::mutex> lk(S->mu);
         S->conn_fds.push_back(cfd);
-        S->conn_threads.emplace_back([S, cfd] { S->connection(cfd); });
+        ++S->active_conns;
+        std::thread([S, cfd] { S->connection(cfd); }).detach();  // a reconnecting worker does not pile up joinable threads
       }
     }
   }
@@ -416,8 +418,10 @@ void ttdps_server_destroy(void* h) {
   }
   S->cv.notify_all();
   if (S->listen_fd >= 0) ::close(S->listen_fd);
-  for (auto& t : S->conn_threads)
-    if (t.joinable()) t.join();
+  {
+    std::unique_lock<std::mutex> lk(S->mu);
+    S->cv.wait(lk, [&] { return S->active_conns == 0; });
+  }
   delete S;
 }
 
