@@ -207,3 +207,48 @@ def test_inspect_cli_lists_and_exports_a_torch_state_dict(tmp_path, capsys):
     assert torch.equal(sd["conv1.weight"][2, 0], torch.from_numpy(tensors["conv1/kernel"][:, :, 0, 2]))
     ema = insp.to_torch_state_dict(insp.resolve_prefix(str(tmp_path)), ema=True)
     assert float(ema["hidden1.weight"].mean()) == 0.5
+
+
+def test_reader_survives_corrupted_index_files(tmp_path):
+    """Truncations, bit flips, 0xff runs and insertions in the .index: the native reader reports an error (or
+    returns checksummed tensors) — it never crashes and never returns silently wrong bytes."""
+    import random
+    import shutil
+    from tensorflow_train_distributed_b200.io import bundle
+    rng = np.random.default_rng(0)
+    tensors = {f"layer{i}/kernel": rng.standard_normal((7 + i, 5)).astype(np.float32) for i in range(40)}
+    prefix = str(tmp_path / "model.ckpt-3")
+    bundle.write_bundle(prefix, tensors)
+    idx = open(prefix + ".index", "rb").read()
+    rnd = random.Random(1234)
+    opened = 0
+    for it in range(150):
+        b = bytearray(idx)
+        mode = it % 4
+        if mode == 0:
+            b = b[:rnd.randrange(len(b))]
+        elif mode == 1:
+            for _ in range(rnd.randrange(1, 8)):
+                b[rnd.randrange(len(b))] ^= 1 << rnd.randrange(8)
+        elif mode == 2:
+            i = rnd.randrange(len(b))
+            b[i:i + 4] = b"\xff\xff\xff\xff"
+        else:
+            i = rnd.randrange(len(b))
+            b = b[:i] + bytes(rnd.randrange(256) for _ in range(rnd.randrange(1, 64))) + b[i:]
+        p2 = str(tmp_path / f"f{it}")
+        open(p2 + ".index", "wb").write(bytes(b))
+        shutil.copy(prefix + ".data-00000-of-00001", p2 + ".data-00000-of-00001")
+        try:
+            with bundle.BundleReader(p2) as r:
+                opened += 1
+                for k in r.keys():
+                    try:
+                        v = r.read(k)
+                    except bundle.BundleError:
+                        continue
+                    if k in tensors and v.shape == tensors[k].shape:  # a tensor that passes its CRC is the original
+                        assert np.array_equal(v, tensors[k]), k
+        except bundle.BundleError:
+            pass
+    assert opened < 150  # the block checksums catch most of it
