@@ -122,3 +122,35 @@ def test_idle_watchdog_ends_serve():
     assert ps.rc == 1  # nobody said goodbye, the idle limit ended serve()
     c.close()
     ps.lib.ttdps_server_destroy(ps.h)
+
+
+def test_server_survives_garbage_and_keeps_serving():
+    """Malformed headers, unknown ops, short and oversized payloads, abrupt closes: the ps neither crashes nor wedges."""
+    import random
+    import socket
+    ps = _Ps(numel=64, n_workers=1, n_agg=1)
+    rnd = random.Random(7)
+    for _ in range(40):
+        s = socket.create_connection(("127.0.0.1", ps.port))
+        s.settimeout(0.05)
+        try:
+            for _ in range(rnd.randrange(1, 4)):
+                op = rnd.choice([0, 1, 2, 3, 4, 6, 8, 9, 77, -1, 2**40])
+                hdr = struct.pack("<4q", op, rnd.choice([0, 1, -5, 2**62, 10**9]), rnd.randrange(-3, 100), 0)
+                s.sendall(hdr[:rnd.choice([32, 32, 32, 7])])
+                s.sendall(bytes(rnd.randrange(256) for _ in range(rnd.choice([0, 0, 13, 256, 512]))))
+                try:
+                    s.recv(4096)
+                except (socket.timeout, ConnectionError):
+                    pass
+        except OSError:
+            pass
+        s.close()
+    c = ps.channel(0)
+    w0 = torch.arange(64, dtype=torch.float32)
+    c.call(0, OP_INIT, 5, payload=torch.cat([w0, w0]))
+    hdr, w = c.call(0, OP_PULL, reply_numel=64)
+    assert int(hdr[1]) == 5 and torch.equal(w, w0)
+    c.call(0, OP_DONE)
+    ps.close()
+    assert ps.rc == 0
