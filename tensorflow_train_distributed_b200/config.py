@@ -104,7 +104,7 @@ class TrainConfig:
     # NVLink fetch lands on the forward's critical path, the broadcast hides behind the barrier), hence off by default.
     fetch_lag: int = 0  # GPU, graph mode: run() returns the values of step s-L, read from the pinned ring the update
     # kernel writes, so the host never waits for the step it just enqueued (0 = the reference's exact per-step fetch;
-    # with L > 0 a stop-at-step check sees global_step L steps late, so up to L extra steps run)
+    # with L > 0 the logged loss / accuracy are L steps old; stop-at-step counts the steps in flight and stays exact)
     write_events: bool = True
     metrics_jsonl: bool = True  # every worker: <checkpoint_dir>/metrics-<task>.jsonl, one line per logging period
     nvtx: bool = False  # NVTX ranges around feed / launch / fetch / checkpoint (Nsight Systems, ncu --nvtx)

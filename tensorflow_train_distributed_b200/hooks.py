@@ -20,6 +20,7 @@ class SessionRunValues:
     loss: float
     accuracy: float
     global_step: int
+    pending: int = 0  # --fetch_lag: steps already enqueued whose global-step increments are not in global_step yet
 
 
 @dataclass
@@ -53,7 +54,9 @@ class StopAtStepHook(SessionRunHook):
             session.request_stop()
 
     def after_run(self, ctx, values) -> None:
-        if values.global_step >= self._last_step:
+        # every step still in flight adds at least one global step (exactly one with sync replicas), so a pipelined
+        # fetch stops on time instead of `fetch_lag` steps late
+        if values.global_step + getattr(values, "pending", 0) >= self._last_step:
             ctx.session.request_stop()
 
     @property

@@ -30,6 +30,7 @@ class StepValues:
     global_step: int
     local_step: int
     learning_rate: float
+    pending: int = 0  # --fetch_lag: steps enqueued after the one these values belong to
 
 
 def hyper_from_config(cfg: TrainConfig, n_replicas: int) -> Hyper:
@@ -268,7 +269,9 @@ class GpuTrainer:
         self._inflight.append(slot)
         if len(self._inflight) > min(lag, self.RING - 2):
             self._last_values = self._wait_slot(self._inflight.popleft())
-        return self._last_values  # before the first pipelined step lands: the state laid down by initialize()
+        # (before the first pipelined step lands these are the values laid down by initialize())
+        import dataclasses as _dc
+        return _dc.replace(self._last_values, pending=len(self._inflight))
 
     def _wait_slot(self, slot: int, timeout_s: float = 30.0) -> StepValues:
         """Poll the pinned ring until the device has written step ``_expect[slot]`` (no CUDA call on the way)."""

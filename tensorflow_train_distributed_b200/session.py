@@ -116,7 +116,7 @@ class MonitoredTrainingSession:
                 break
             except TransportError:
                 self._recover()
-        values = SessionRunValues(float(v.loss), float(v.accuracy), int(v.global_step))
+        values = SessionRunValues(float(v.loss), float(v.accuracy), int(v.global_step), int(getattr(v, "pending", 0)))
         for h in self._hooks:
             h.after_run(ctx, values)
         self._local_step += 1

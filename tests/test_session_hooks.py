@@ -150,3 +150,25 @@ def test_nvtx_range_is_a_noop_without_cuda():
         pass
     tracing.enable_nvtx(False)
     assert not tracing.nvtx_enabled()
+
+
+def test_stop_at_step_counts_steps_in_flight():
+    """--fetch_lag: values lag, but every enqueued step will add >= 1 global step, so the stop comes on time."""
+    from tensorflow_train_distributed_b200.hooks import SessionRunContext, SessionRunValues, StopAtStepHook
+
+    class _S:
+        stopped = False
+
+        def global_step(self):
+            return 0
+
+        def request_stop(self):
+            self.stopped = True
+
+    s = _S()
+    h = StopAtStepHook(last_step=10)
+    h.after_create_session(s)
+    h.after_run(SessionRunContext(s, 0), SessionRunValues(1.0, 0.5, 5, pending=4))
+    assert not s.stopped
+    h.after_run(SessionRunContext(s, 1), SessionRunValues(1.0, 0.5, 6, pending=4))
+    assert s.stopped
