@@ -58,3 +58,28 @@ def test_python_queue_reader_delivers_batches():
             assert tuple(x.shape) == (128, 784) and tuple(y.shape) == (128,)
     finally:
         q.close()
+
+
+@pytest.mark.parametrize("gz", [False, True])
+def test_mnist_idx_files_load_like_read_data_sets(tmp_path, gz):
+    """``--data idx``: the loader of real MNIST files (distribute_training.py:184) — idx3/idx1 big-endian headers,
+    plain or gzipped, images scaled to [0,1] and flattened, the first 5000 examples held out for validation."""
+    import gzip
+    import struct
+    from tensorflow_train_distributed_b200.data import load_mnist_idx, make_dataset
+    rng = np.random.default_rng(0)
+    n = 5200
+    imgs = rng.integers(0, 256, size=(n, 28, 28), dtype=np.uint8)
+    labs = rng.integers(0, 10, size=n, dtype=np.uint8)
+    opener = gzip.open if gz else open
+    ext = ".gz" if gz else ""
+    with opener(tmp_path / ("train-images-idx3-ubyte" + ext), "wb") as f:
+        f.write(struct.pack(">IIII", 0x00000803, n, 28, 28) + imgs.tobytes())
+    with opener(tmp_path / ("train-labels-idx1-ubyte" + ext), "wb") as f:
+        f.write(struct.pack(">II", 0x00000801, n) + labs.tobytes())
+    ds = load_mnist_idx(str(tmp_path), seed=1)
+    assert ds.num_examples == 200 and ds.images.shape == (200, 784) and ds.images.dtype == np.float32
+    assert np.allclose(ds.images[0], imgs[5000].reshape(-1) / 255.0) and ds.labels[3] == labs[5003]
+    assert 0.0 <= ds.images.min() and ds.images.max() <= 1.0 and ds.labels.dtype == np.int64
+    x, y = make_dataset("idx", str(tmp_path), 0, 784, 10, seed=1).next_batch(64)
+    assert x.shape == (64, 784) and y.shape == (64,)
