@@ -69,7 +69,7 @@ class DataSet:
 
 
 def synthetic_mnist(num_examples: int = 55000, input_dim: int = 784, num_classes: int = 10, seed: int = 0,
-                    noise: float = 0.35) -> DataSet:
+                    noise: float = 0.35, shuffle_seed: Optional[int] = None) -> DataSet:
     """Class-conditional synthetic images: each class is a fixed sparse stroke pattern, each example that pattern
     at random intensity plus uniform noise, clipped to [0, 1]."""
     rng = np.random.default_rng(seed)
@@ -78,7 +78,7 @@ def synthetic_mnist(num_examples: int = 55000, input_dim: int = 784, num_classes
     gain = rng.uniform(0.5, 1.0, size=(num_examples, 1)).astype(np.float32)
     images = templates[labels] * gain + noise * rng.random((num_examples, input_dim), dtype=np.float32)
     np.clip(images, 0.0, 1.0, out=images)
-    return DataSet(images, labels, seed=seed + 1)
+    return DataSet(images, labels, seed=seed + 1 if shuffle_seed is None else shuffle_seed)
 
 
 def _read_idx(path: str) -> np.ndarray:
@@ -90,7 +90,7 @@ def _read_idx(path: str) -> np.ndarray:
         return np.frombuffer(f.read(), dtype=np.uint8).reshape(dims)
 
 
-def load_mnist_idx(data_path: str, seed: int = 0, validation_size: int = 5000) -> DataSet:
+def load_mnist_idx(data_path: str, seed: int = 0, validation_size: int = 5000) -> DataSet:  # seed: shuffle order
     """Real MNIST from idx files, split like ``read_data_sets`` (55000 train after 5000 validation)."""
     def find(stem: str) -> str:
         for ext in ("", ".gz"):
@@ -103,11 +103,14 @@ def load_mnist_idx(data_path: str, seed: int = 0, validation_size: int = 5000) -
     return DataSet(images[validation_size:], labels[validation_size:], seed=seed)
 
 
-def make_dataset(kind: str, data_path: str, num_examples: int, input_dim: int, num_classes: int, seed: int) -> DataSet:
+def make_dataset(kind: str, data_path: str, num_examples: int, input_dim: int, num_classes: int, seed: int,
+                 shuffle_seed: Optional[int] = None) -> DataSet:
+    """``seed`` fixes the CONTENT of a synthetic set (every worker must see the same one, as with MNIST, :184);
+    ``shuffle_seed`` the order in which this worker walks it."""
     if kind == "idx":
-        return load_mnist_idx(data_path, seed)
+        return load_mnist_idx(data_path, seed if shuffle_seed is None else shuffle_seed)
     if kind == "synthetic":
-        return synthetic_mnist(num_examples, input_dim, num_classes, seed)
+        return synthetic_mnist(num_examples, input_dim, num_classes, seed, shuffle_seed=shuffle_seed)
     raise ValueError(f"unknown data kind {kind!r}")
 
 

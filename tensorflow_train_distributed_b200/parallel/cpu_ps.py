@@ -68,8 +68,8 @@ class CpuMlp:
         self.layout, self.activation, self.dropout_rate = layout, activation, dropout_rate
         self.gen = torch.Generator().manual_seed(seed)
 
-    def loss_and_grads(self, params: Dict[str, torch.Tensor], x: torch.Tensor, y: torch.Tensor):
-        leaves = {k: v.detach().clone().requires_grad_(True) for k, v in params.items()}
+    def logits(self, leaves: Dict[str, torch.Tensor], x: torch.Tensor, training: bool = True) -> torch.Tensor:
+        """``forward_propagation`` (:39-63); the reference hard-codes training=True (:94), evaluation turns dropout off."""
         h = x
         groups = self.layout.groups
         for i, g in enumerate(groups):
@@ -93,10 +93,15 @@ class CpuMlp:
                     h = torch.nn.functional.elu(h)
                 elif self.activation == "relu":
                     h = torch.relu(h)
-                if self.dropout_rate > 0:  # always training=True (:94)
+                if self.dropout_rate > 0 and training:
                     keep = 1.0 - self.dropout_rate
                     mask = (torch.rand(h.shape, generator=self.gen) < keep).to(h.dtype) / keep
                     h = h * mask
+        return h
+
+    def loss_and_grads(self, params: Dict[str, torch.Tensor], x: torch.Tensor, y: torch.Tensor):
+        leaves = {k: v.detach().clone().requires_grad_(True) for k, v in params.items()}
+        h = self.logits(leaves, x, training=True)  # always training=True (:94)
         loss = torch.nn.functional.cross_entropy(h, y)
         loss.backward()
         zl = h.gather(1, y.view(-1, 1))

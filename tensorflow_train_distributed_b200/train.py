@@ -57,8 +57,9 @@ def run_worker(cfg: TrainConfig, cluster: cl.ClusterSpec, transport: str) -> int
     task = cl.resolve_task(cluster, "worker", cfg.task_id, transport)
     is_chief = task.is_chief  # :183
     layout = build_layout(cfg)
-    dataset = make_dataset(cfg.data, cfg.data_path, cfg.dataset_size, cfg.input_dim, cfg.num_classes,
-                           cfg.seed + 1000 * (cfg.task_id + 1))  # every worker loads the full set (:184)
+    # every worker loads the SAME full set (:184) and walks it in its own order
+    dataset = make_dataset(cfg.data, cfg.data_path, cfg.dataset_size, cfg.input_dim, cfg.num_classes, cfg.seed + 1000,
+                           shuffle_seed=cfg.seed + 1000 * (cfg.task_id + 1) + 1)
 
     if transport == "gloo":
         from .parallel.cpu_ps import PsWorkerTrainer, init_gloo

@@ -194,3 +194,21 @@ def test_cluster_launcher_spawns_every_task(tmp_path):
     finals = re.findall(r"\[worker:(\d)\] .*total step: (\d+), global_step: (\d+)", out)
     assert len(finals) == 2 and all(int(g) >= 80 for _, _, g in finals)
     assert "ps 0 done" in out
+
+
+@pytest.mark.timeout(300)
+def test_evaluate_cli_scores_a_trained_checkpoint(tmp_path):
+    """Train on the CPU tier, then ``python -m ...evaluate``: dropout off, weights or moving averages, same data set."""
+    d = str(tmp_path / "ck")
+    outs = _launch(1, 2, ["--training_steps=300", "--save_checkpoint_secs=none", "--save_checkpoint_steps=100", "--transport=tcp"], d)
+    for k, (rc, out) in outs.items():
+        assert rc == 0, (k, out[-3000:])
+    env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="1")
+    for extra in ([], ["--ema"]):
+        r = subprocess.run([sys.executable, "-m", "tensorflow_train_distributed_b200.evaluate", f"--checkpoint_dir={d}",
+                            "--dataset_size=4096"] + extra, env=env, cwd=ROOT, capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, (r.stdout + r.stderr)[-2000:]
+        m = re.search(r"global_step (\d+), (\d+) examples, loss ([0-9.e+-]+), accuracy ([0-9.]+)", r.stdout)
+        assert m, r.stdout
+        assert int(m.group(1)) >= 300 and int(m.group(2)) == 4096
+        assert float(m.group(3)) < 0.5 and float(m.group(4)) > 0.95
