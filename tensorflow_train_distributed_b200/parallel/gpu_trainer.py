@@ -48,7 +48,7 @@ class GpuTrainer:
 
     def __init__(self, cfg: TrainConfig, device_index: int = 0, comm=None):
         if not torch.cuda.is_available():
-            raise RuntimeError("GpuTrainer needs a CUDA device; use the gloo transport on CPU-only machines")
+            raise RuntimeError("GpuTrainer needs a CUDA device; use --device cpu (tcp or gloo transport) on CPU-only machines")
         self.cfg, self.comm = cfg, comm
         self.device = torch.device("cuda", device_index)
         torch.cuda.set_device(self.device)
