@@ -120,3 +120,22 @@ def test_console_format_matches_reference():
     s = tlog.format_step(100, 201, 0.25, 0.9375, 0.0123)
     assert s == "After 100 training steps (201 global steps), loss on training batch is 0.25, accuracy is 0.9375. (0.012 sec/batch)"
     assert tlog.format_final(1000, 2000) == "total step: 1000, global_step: 2000"
+
+
+def test_flat_plan_for_every_world_size_and_model():
+    """1..8 owners x (reference MLP, wide MLP, LeNet): ranges cover the buffer in order, every owner holds something,
+    boundaries are 64-element aligned (the update kernel's 128-bit path needs 4) and balanced to one snap unit."""
+    layouts = {"mlp": sharding.ParamLayout(sharding.mlp_groups(784, [200, 100, 50, 25, 10])),
+               "wide": sharding.ParamLayout(sharding.mlp_groups(784, [8192, 8192, 10])),
+               "lenet": sharding.ParamLayout(sharding.lenet_groups())}
+    for name, layout in layouts.items():
+        g0 = layout.groups[0]
+        unit = max(64 * g0.cols, 64)
+        for n in range(1, 9):
+            p = sharding.flat(layout, n)
+            assert len(p.bounds) == n + 1 and p.bounds[0] == 0 and p.bounds[-1] == layout.total, (name, n)
+            sizes = [p.bounds[i + 1] - p.bounds[i] for i in range(n)]
+            assert all(s > 0 for s in sizes), (name, n, sizes)
+            assert all(b % 4 == 0 for b in p.bounds[1:-1]), (name, n)
+            assert max(sizes) - min(sizes) <= 2 * unit + 64, (name, n, sizes)
+            assert [p.owner_of(b) for b in p.bounds[:-1]] == list(range(n))
