@@ -57,6 +57,9 @@ class GpuTrainer:
         self.sync = cfg.sync_replicas or self.world == 1
         self.stream = torch.cuda.Stream(device=self.device)
         self.layout: ParamLayout = self._build_layout()
+        if self.sync and cfg.replicas_to_aggregate not in (0, self.world):
+            raise ValueError(f"--replicas_to_aggregate={cfg.replicas_to_aggregate}: the GPU sync path aggregates exactly one "
+                             f"gradient per replica ({self.world}); N-of-M aggregation exists in the CPU tier (--device cpu)")
         n_agg = (cfg.replicas_to_aggregate or self.world) if self.sync else 1
         self.hyper = hyper_from_config(cfg, n_agg)
         with torch.cuda.stream(self.stream):
