@@ -154,3 +154,23 @@ def test_server_survives_garbage_and_keeps_serving():
     c.call(0, OP_DONE)
     ps.close()
     assert ps.rc == 0
+
+
+def test_one_of_two_aggregation_drops_the_slower_replica():
+    """replicas_to_aggregate=1, total_num_replicas=2 (backup-worker mode): the first fresh gradient moves the step,
+    the slower replica's gradient for the same step is stale; two tokens per step keep both workers going."""
+    ps = _Ps(numel=2, n_workers=2, n_agg=1, use_ema=0)
+    a, b = ps.channel(0), ps.channel(1)
+    a.call(0, OP_INIT, 0, payload=torch.zeros(4))
+    a.call(0, OP_SYNC_INIT, 1)
+    g = torch.tensor([1.0, 2.0])
+    hdr, _ = a.call(0, OP_PUSH_SYNC, _lr_bits(1.0), 0, payload=g)
+    assert int(hdr[1]) == 1
+    hdr, _ = b.call(0, OP_PUSH_SYNC, _lr_bits(1.0), 0, payload=10 * g)
+    assert int(hdr[1]) == 1 and ps.stats()["dropped"] == 1
+    _, w = a.call(0, OP_PULL, reply_numel=2)
+    assert torch.equal(w, -g)
+    toks = sorted(int(c.call(0, OP_TOKEN)[0][1]) for c in (a, b, a))
+    assert toks == [0, 1, 1]  # one pre-loaded token + max(total, aggregate) = 2 for the new step
+    a.call(0, OP_DONE), b.call(0, OP_DONE)
+    ps.close()
