@@ -73,7 +73,6 @@ class TrainConfig:
     regularizer: str = "l2"  # none | l1 | l2 — the script builds L1 (:50) that never reaches the loss; north-star asks L2
     regularizer_scale: float = 0.01  # :39
     use_moving_average: bool = True  # north-star; the reference's EMA block is dead code (:153-161)
-    ema_chief_only: bool = False  # the dead code applied the EMA on the chief only (:154)
     replicas_to_aggregate: int = 0  # 0 -> number of workers (:146)
     total_num_replicas: int = 0  # 0 -> number of workers (:147)
     save_checkpoint_secs: Optional[float] = 60.0  # :213; None -> events only (:213-214)
@@ -110,7 +109,6 @@ class TrainConfig:
     nvtx: bool = False  # NVTX ranges around feed / launch / fetch / checkpoint (Nsight Systems, ncu --nvtx)
     inject_fault: str = ""  # "step=N,rank=R" test hook (kill -> resume)
     rendezvous_timeout_secs: float = 120.0
-    stop_grace_period_secs: float = 120.0
     ps_idle_timeout_secs: float = 0.0  # >0: a ps exits after this long without worker traffic (reference: never, :181)
 
     # ------------------------------------------------------------------ derived values
