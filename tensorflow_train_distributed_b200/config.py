@@ -86,7 +86,7 @@ class TrainConfig:
     device: str = "auto"  # auto | cuda | cpu
     transport: str = "auto"  # auto | nvlink (symmetric memory on GPUs) | gloo (ps processes on CPU, torch.distributed)
     # | tcp (ps processes on CPU: native C++ server on every --ps_hosts endpoint, csrc/io/ps_server.cc)
-    sharding: str = "auto"  # auto | flat | round_robin
+    sharding: str = "auto"  # auto | flat (GPU store: 1/N ranges of the flat buffer) | round_robin (ps processes)
     seed: int = 1234
     data: str = "synthetic"  # synthetic | idx (MNIST idx files under data_path)
     dataset_size: int = 55000  # size of the TF train split

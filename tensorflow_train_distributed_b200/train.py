@@ -154,6 +154,11 @@ def main(argv: Optional[Sequence[str]] = None) -> int:
         except Exception:  # noqa: BLE001
             cuda = False
     transport = cl.choose_transport(cfg, cuda)
+    # --sharding: the GPU store owns contiguous 1/N ranges of one flat buffer (flat); real ps processes hold whole
+    # variables placed round-robin (the reference's replica_device_setter). Asking for the other one is an error.
+    want = {"nvlink": "flat"}.get(transport, "round_robin")
+    if cfg.sharding not in ("auto", want):
+        raise SystemExit(f"--sharding={cfg.sharding} is not available with the {transport} transport (it uses {want})")
     if cfg.job_name == "ps":
         return run_ps(cfg, cluster, transport)
     return run_worker(cfg, cluster, transport)
