@@ -242,7 +242,11 @@ struct Server {
         std::unique_lock<std::mutex> lk(mu);
         touch();
         const int64_t epoch0 = release_epoch;
-        cv.wait(lk, [&] { return stopping || !tokens.empty() || release_epoch != epoch0; });
+        // A worker that already sent DONE contributes no more gradients, so with n_agg == n_workers no further
+        // aggregate can complete: a token request that arrives AFTER that DONE (a restarted worker, uneven stop
+        // timing) must not wait for one. It gets the current global_step at once and reaches its stop check.
+        const bool nobody_left = !done_workers.empty() && tokens.empty();
+        cv.wait(lk, [&] { return nobody_left || stopping || !tokens.empty() || release_epoch != epoch0; });
         if (!tokens.empty()) {
           reply[1] = tokens.front();
           tokens.pop_front();

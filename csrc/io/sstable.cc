@@ -126,7 +126,9 @@ std::string TableBuilder::finish() {
 // reader
 // ------------------------------------------------------------------------------------------------
 static bool read_block(const std::string& file, uint64_t off, uint64_t size, std::string* contents) {
-  if (off + size + kBlockTrailerSize > file.size()) {
+  // (written so that a corrupt handle with off/size near 2^64 cannot wrap the sum around)
+  if (file.size() < kBlockTrailerSize || size > file.size() - kBlockTrailerSize ||
+      off > file.size() - kBlockTrailerSize - size) {
     set_error("sstable: block handle points outside the file");
     return false;
   }

@@ -19,6 +19,7 @@
 // bias [cols], i.e. a [rows+1, cols] matrix, which is also exactly what the wgrad GEMM writes.
 #include <atomic>
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../include/ttd_b200.h"
@@ -56,6 +57,8 @@ struct PeerInfo {
   TtdStepState* state0;              // step state of the owner of global_step (shard 0)
   int n_owners;
   int trace_all;                     // diagnostic: phase clocks as the maximum over all CTAs (TtdPeers.reserved bit0)
+  int force_scalar;                  // [lo,hi) cuts a 4-element group of a vector-path variable: take the scalar path
+  unsigned long long watchdog_ns;    // a replica barrier that waits longer than this traps (ttd_set_barrier_timeout_ms)
 };
 
 enum { kInit = 0, kRefresh = 1, kUpdate = 2, kAsyncPull = 3, kAsyncPush = 4 };
@@ -109,7 +112,7 @@ __device__ __forceinline__ void replica_barrier(const PeerInfo& pi, uint32_t epo
       if ((++spins & 0x3FFu) == 0) {  // watchdog: a dead peer raises instead of hanging the GPU
         const uint64_t now = globaltimer_ns();
         if (t0 == 0) t0 = now;
-        else if (now - t0 > 20000000000ull) __trap();
+        else if (now - t0 > pi.watchdog_ns) __trap();
       }
     }
   }
@@ -365,7 +368,7 @@ __global__ void __launch_bounds__(256, 4) param_kernel(const __grid_constant__ V
     if (t_hi <= lo || t_lo >= hi) continue;
 
     __syncthreads();  // previous tile's transposed reads are done
-    if (MODE == kUpdate && (C & 3) == 0) {
+    if (MODE == kUpdate && (C & 3) == 0 && !pi.force_scalar) {
       // ---- vector tile (row pitch a multiple of 4): 128-bit traffic end to end ----------------------------
       // thread -> rows tid/8 and tid/8+32, four columns at 4*(tid%8); both rows' loads are issued before any
       // arithmetic. Gradients: ONE multimem.ld_reduce per group (the NVSwitch adds the replicas' values in
@@ -736,6 +739,23 @@ static int build_table(VarTable* vt, const TtdVarDesc* vars, int nvars, long lon
   return 0;
 }
 
+// How long a replica may sit in a cross-GPU barrier before the kernel traps. A trap destroys the CUDA context, so
+// the limit has to outlast anything a peer may legitimately do between two steps — above all the chief writing
+// a checkpoint (export + crc32c + file system) while the others already wait in the barrier-in of their next update.
+static std::atomic<unsigned long long> g_barrier_timeout_ns{0};
+static unsigned long long barrier_timeout_ns() {
+  unsigned long long v = g_barrier_timeout_ns.load();
+  if (v == 0) {
+    v = 600ull * 1000000000ull;  // default: 10 minutes
+    if (const char* e = getenv("TTD_BARRIER_TIMEOUT_SECS")) {
+      const double s = atof(e);
+      if (s > 0.0) v = static_cast<unsigned long long>(s * 1e9);
+    }
+    g_barrier_timeout_ns.store(v);
+  }
+  return v;
+}
+
 static int grid_for(int total_tiles) {
   const int cap = 148 * 8;
   return total_tiles < cap ? total_tiles : cap;
@@ -744,6 +764,10 @@ static int grid_for(int total_tiles) {
 }  // namespace ttd
 
 using namespace ttd;
+
+extern "C" void ttd_set_barrier_timeout_ms(uint64_t ms) {
+  g_barrier_timeout_ns.store(ms == 0 ? 0ull : static_cast<unsigned long long>(ms) * 1000000ull);
+}
 
 extern "C" int ttd_init_params(float* w, float* ema, const TtdVarDesc* vars, int nvars, uint64_t seed,
                                void* stream) {
@@ -784,6 +808,8 @@ extern "C" int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars, in
                                 const TtdHyper* hyper, const TtdPeers* peers, TtdStepState* state,
                                 int32_t bump_global_step, void* stream) {
   VarTable vt;
+  if (hi < 0 && nvars >= 1 && nvars <= kMaxVars)  // negative hi: up to the end of the last group
+    hi = vars[nvars - 1].offset + static_cast<int64_t>(vars[nvars - 1].rows + 1) * vars[nvars - 1].cols;
   int rc = build_table(&vt, vars, nvars, lo, hi);
   if (rc) return rc;
   if (peers == nullptr || peers->n_grads < 1 || peers->n_grads > kMaxPeers || peers->n_copies < 1 ||
@@ -805,6 +831,14 @@ extern "C" int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars, in
   pi.rank = peers->rank;
   pi.barrier = peers->barrier;
   pi.trace_all = peers->reserved & 1;
+  pi.watchdog_ns = barrier_timeout_ns();
+  // The 128-bit path updates whole 4-element groups; a range boundary inside such a group (possible only for
+  // callers that pick their own [lo, hi): the flat plan's bounds are multiples of 4) selects the scalar path.
+  for (int i = 0; i < nvars && hi >= 0; ++i) {
+    if (vars[i].cols % 4 != 0) continue;
+    const long long v_lo = vars[i].offset, v_hi = v_lo + static_cast<long long>(vars[i].rows + 1) * vars[i].cols;
+    if ((lo > v_lo && lo < v_hi && ((lo - v_lo) & 3)) || (hi > v_lo && hi < v_hi && ((hi - v_lo) & 3))) pi.force_scalar = 1;
+  }
   int grid = grid_for(vt.tile_begin[vt.n] > 0 ? vt.tile_begin[vt.n] : 1);
   if (pi.barrier) {
     // blocks of different replicas wait on one another: all of them must be resident at once

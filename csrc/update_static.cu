@@ -24,6 +24,8 @@
 //   * The first call on each GPU performs the one-time set-up (it asks the runtime for the device
 //     address of the array with cudaGetSymbolAddress while that GPU is current). Make that first call
 //     before starting any stream capture.
+//   * The call must run outside stream capture: the variable table is copied from the caller's host array on
+//     every call, and a captured copy would re-read that array at each replay. Captured streams are refused.
 //   * No cudaMalloc, cudaFree, or other allocating routine is called — by this file or on its behalf.
 #include <atomic>
 #include <math.h>
@@ -143,6 +145,21 @@ __global__ void __launch_bounds__(256) update_static_kernel(unsigned char* __res
     st->metrics_acc[0] = 0.0f;
     st->metrics_acc[1] = 0.0f;
     __threadfence();
+    if (h.host_mirror != nullptr && h.mirror_slots > 0) {
+      // same pinned-ring mirror as the regular kernel (tagged 16-byte chunks, see param_store.cu)
+      const uint4* src = reinterpret_cast<const uint4*>(st);
+      uint4* dst = reinterpret_cast<uint4*>(static_cast<TtdStepState*>(h.host_mirror) +
+                                            (st->local_step - 1) % static_cast<uint64_t>(h.mirror_slots));
+      const uint32_t tag = static_cast<uint32_t>(st->local_step);
+      uint4 c1 = src[1], c2 = src[2], c3 = src[3];
+      c1.x = tag;
+      c2.x = tag;
+      c3.w = tag;
+      dst[1] = c1;
+      dst[2] = c2;
+      dst[3] = c3;
+      dst[0] = src[0];
+    }
   }
 }
 
@@ -164,10 +181,23 @@ extern "C" int ttd_apply_update_static(float* w, float* ema, const float* grad, 
     set_error("ttd_apply_update_static: w, grad, vars, hyper and state must be non-NULL");
     return -1;
   }
+  if (hi < 0)  // same convention as ttd_apply_update: a negative hi means "up to the end of the last group"
+    hi = vars_host[nvars - 1].offset + static_cast<int64_t>(vars_host[nvars - 1].rows + 1) * vars_host[nvars - 1].cols;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  {
+    // The variable table travels by cudaMemcpyAsync from the caller's (pageable) array. Inside a stream capture
+    // that copy would become a graph node that re-reads the host array on every replay, long after the caller
+    // has released it: refuse instead.
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cap) == cudaSuccess && cap != cudaStreamCaptureStatusNone) {
+      set_error("ttd_apply_update_static: the stream is being captured; this entry point copies its variable table "
+                "from host memory on every call and must run outside stream capture");
+      return -1;
+    }
+  }
   unsigned char* scratch = nullptr;
   int rc = scratch_for_current_device(&scratch);  // first call on this GPU resolves the address
   if (rc != 0) return rc;
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
   // The array still holds the previous call's bytes: zero the counter block, overwrite the table slots in use.
   TTD_CUDA(cudaMemsetAsync(scratch, 0, kCounterBytes, s));
   TTD_CUDA(cudaMemcpyAsync(scratch + kTableOffset, vars_host, sizeof(TtdVarDesc) * static_cast<size_t>(nvars),

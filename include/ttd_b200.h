@@ -164,6 +164,8 @@ typedef struct TtdPeers {
  *   w -= lr*g ; ema -= (1-d)(ema-w) ; bf16 copies refreshed on every replica in `peers`
  *   last CTA: ++global_step (if bump_global_step bit0), ++local_step, metrics_out <- metrics_acc <- 0.
  *   bump_global_step bit1: launch with programmatic dependent launch.
+ * hi < 0: up to the end of the last group. lo/hi need no alignment (a boundary inside a 4-element group of a
+ * variable whose row pitch is a multiple of 4 selects the element-wise path for the whole launch).
  * Reference :136-140 (lr), :150-152 (apply + global_step), :153-161 (EMA), :50-55 (regulariser),
  * :144-148 (SyncReplicasOptimizer mean-of-N aggregation when n_grads > 1). */
 int ttd_apply_update(float* w, float* ema, const TtdVarDesc* vars_host, int nvars, int64_t lo, int64_t hi,
@@ -288,11 +290,18 @@ int ttd_feeder_step(void* feeder, void* graph_exec, const void* host_x, const vo
  * TTD_STATIC_MAX_VARS groups per call; more is refused with an error and nothing is launched.
  * state->done_counter is not used. All calls on a GPU share that array: calls whose kernels could overlap
  * on the GPU race and must be ordered by the caller. The first call on each GPU looks up the array's
- * device address (cudaGetSymbolAddress); make it before any stream capture begins. */
+ * device address (cudaGetSymbolAddress); make it before any stream capture begins. The call itself is refused
+ * on a capturing stream (it copies the table from host memory every time). hi < 0 means "to the end of the last
+ * group", as in ttd_apply_update; hyper->host_mirror is honoured the same way. lo/hi need no alignment. */
 #define TTD_STATIC_MAX_VARS 64
 int ttd_apply_update_static(float* w, float* ema, const float* grad, const TtdVarDesc* vars_host, int nvars,
                             int64_t lo, int64_t hi, const TtdHyper* hyper_host, TtdStepState* state,
                             int32_t bump_global_step, void* stream);
+
+/* Cross-GPU barrier watchdog: a replica that waits longer than this inside the update kernel's barriers traps
+ * (which destroys its CUDA context) instead of hanging the GPU. Default 600 s, or TTD_BARRIER_TIMEOUT_SECS; it must
+ * outlast the chief's checkpoint writes, during which the other replicas already wait in their next update. */
+void ttd_set_barrier_timeout_ms(uint64_t ms);
 
 /* Rewrite only the bf16 compute copies from the fp32 master (after a restore). */
 int ttd_refresh_copies(const float* w, const TtdVarDesc* vars_host, int nvars, void* stream);

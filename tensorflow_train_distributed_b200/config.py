@@ -109,6 +109,10 @@ class TrainConfig:
     nvtx: bool = False  # NVTX ranges around feed / launch / fetch / checkpoint (Nsight Systems, ncu --nvtx)
     inject_fault: str = ""  # "step=N,rank=R" test hook (kill -> resume)
     rendezvous_timeout_secs: float = 120.0
+    barrier_timeout_secs: float = 600.0  # GPU sync replicas: a replica that waits longer than this for its peers inside
+    # the update kernel traps (dead-peer detection). Must outlast the chief's checkpoint writes.
+    max_restarts: int = 0  # launcher only: relaunch the whole worker group this many times when a worker dies; the
+    # new processes resume from the newest checkpoint in --checkpoint_dir (the GPU tier's _RecoverableSession)
     ps_idle_timeout_secs: float = 0.0  # >0: a ps exits after this long without worker traffic (reference: never, :181)
 
     # ------------------------------------------------------------------ derived values

@@ -239,6 +239,8 @@ def load(build_if_missing: bool = True) -> C.CDLL:
                                       C.c_int64, C.c_void_p]
     lib.ttd_mlp_tail.restype = C.c_int
     lib.ttd_mlp_tail.argtypes = [C.POINTER(TailDesc), C.c_uint64, C.c_uint32, C.c_void_p]
+    lib.ttd_set_barrier_timeout_ms.restype = None
+    lib.ttd_set_barrier_timeout_ms.argtypes = [C.c_uint64]
     lib.ttd_copy_d2d.restype = C.c_int
     lib.ttd_copy_d2d.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     _lib = lib

@@ -281,8 +281,12 @@ class PsServer:
                             self._issue_tokens()
                 _send(src, OP_PUSH_SYNC, self.global_step)
             elif op == OP_TOKEN:
-                self.pending_tokens.append(src)
-                self._issue_tokens()
+                if self.done_workers and not self.tokens:
+                    # a worker has already left, so no further aggregate can complete: answer at once
+                    _send(src, OP_TOKEN, self.global_step, self.global_step)
+                else:
+                    self.pending_tokens.append(src)
+                    self._issue_tokens()
             elif op == OP_GET_STATE:
                 _send(src, OP_GET_STATE, self.global_step, payload=torch.cat([self.w, self.ema]))
             elif op == OP_DONE:

@@ -45,6 +45,10 @@ class GpuTrainer:
     """One process per GPU. ``comm`` (a SymmetricComm) joins several of them into one parameter server."""
 
     RING = 64  # pinned result slots for asynchronous per-step fetches
+    # Every worker reads the checkpoint itself (reference :208-215: after the chief's restore EVERY variable on
+    # EVERY ps holds the restored value). Each GPU is the ps of one flat range and keeps its own global_step, so
+    # a restore that reached only the chief would leave the other owners on their seed-initialised shards.
+    every_rank_restores = True
 
     def __init__(self, cfg: TrainConfig, device_index: int = 0, comm=None):
         if not torch.cuda.is_available():
@@ -85,6 +89,7 @@ class GpuTrainer:
             self.model.set_device_dataset(self._feed_x, self._feed_y)
         self.copy_stream = torch.cuda.Stream(device=self.device)
         self.lib = N.load()
+        self.lib.ttd_set_barrier_timeout_ms(int(max(1.0, cfg.barrier_timeout_secs) * 1000))
         self._feeder = self.lib.ttd_feeder_create(
             self.stream.cuda_stream, self.copy_stream.cuda_stream, self._feed_x[0].data_ptr(), self._feed_x[1].data_ptr(),
             self._feed_y[0].data_ptr(), self._feed_y[1].data_ptr(), self._feed_x[0].numel() * 4, self._feed_y[0].numel() * 8)
@@ -151,6 +156,7 @@ class GpuTrainer:
             if self.comm is not None:
                 self.comm.reset_flags(self.store)
                 self.comm.barrier()
+                self._check_replicas_agree(restore is not None)
         self._steps_enqueued = 0  # mirrors the device's local_step (which slot of the feed pool a step reads)
         self._pinned_state.zero_()  # entries of the warm-up step (or of an earlier run) must not pass for new ones
         if self.cfg.cuda_graph:
@@ -158,6 +164,27 @@ class GpuTrainer:
         self._inflight.clear()
         self._last_values = self.read_values()  # global_step of a restored checkpoint, zeros otherwise
         self._initialized = True
+
+    def _check_replicas_agree(self, restored: bool) -> None:
+        """All replicas must start from the same global_step and the same parameters (a replica that missed the
+        restore would otherwise train on with a different learning rate and stop at a different step)."""
+        import torch.distributed as dist
+        digest = torch.stack([self.store.state[0].double(), torch.tensor(1.0 if restored else 0.0, device=self.device,
+                                                                         dtype=torch.float64),
+                              self.store.w.double().sum(), self.store.ema.double().sum()])
+        all_d = [torch.zeros_like(digest) for _ in range(self.world)]
+        dist.all_gather(all_d, digest)
+        if not all(torch.equal(all_d[0], d) for d in all_d):
+            raise RuntimeError("replicas disagree after initialisation (global_step, restored?, sum(w), sum(ema)): "
+                               + "; ".join(str(d.tolist()) for d in all_d))
+
+    def reconnect(self, restore: Optional[Dict[str, np.ndarray]] = None) -> None:
+        """Session recovery (``_RecoverableSession``): lay the state down again — from the newest checkpoint when
+        there is one — and re-capture the step. All replicas have to call it together (it contains barriers)."""
+        self.stream.synchronize()
+        self._graph = None
+        self._graph_exec = None
+        self.initialize(restore=restore)
 
     def _capture(self) -> None:
         g = torch.cuda.CUDAGraph()

@@ -139,7 +139,7 @@ class MonitoredTrainingSession:
             raise TransportError(f"giving up after {self._max_recoveries} recoveries")
         time.sleep(min(2.0, 0.2 * self._recoveries))
         restore = None
-        if self.checkpoint_dir and self.is_chief:
+        if self.checkpoint_dir and (self.is_chief or getattr(self.trainer, "every_rank_restores", False)):
             prefix = ckpt.latest_checkpoint(self.checkpoint_dir)
             if prefix is not None:
                 from .io import bundle

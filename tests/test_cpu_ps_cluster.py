@@ -197,6 +197,28 @@ def test_cluster_launcher_spawns_every_task(tmp_path):
 
 
 @pytest.mark.timeout(300)
+def test_launcher_restarts_the_group_after_a_worker_dies(tmp_path):
+    """``--max_restarts``: the launcher is the supervisor of the recoverable session (:208). Worker 1 is killed at
+    its 60th local step; the group is stopped, started again, restores the newest checkpoint and finishes."""
+    ports = _free_ports(3)
+    d = tmp_path / "ck"
+    cmd = [sys.executable, "-m", "tensorflow_train_distributed_b200.launch", f"--ps_hosts=127.0.0.1:{ports[0]}",
+           f"--worker_hosts=127.0.0.1:{ports[1]},127.0.0.1:{ports[2]}", "--device=cpu", "--transport=tcp", "--sync_replicas",
+           "--dataset_size=2048", "--training_steps=150", "--save_checkpoint_secs=none", "--save_checkpoint_steps=25",
+           "--log_every_n_steps=20", f"--checkpoint_dir={d}", "--max_restarts=1", "--inject_fault=step=60,rank=1",
+           "--ps_idle_timeout_secs=20"]
+    env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="1", MKL_NUM_THREADS="1")
+    r = subprocess.run(cmd, env=env, cwd=ROOT, capture_output=True, text=True, timeout=280)
+    out = r.stdout
+    assert r.returncode == 0, (out + r.stderr)[-3000:]
+    assert "restarting the group from the newest checkpoint (restart 1 of 1)" in out
+    finals = re.findall(r"\[worker:(\d)\] .*total step: (\d+), global_step: (\d+)", out)
+    assert len(finals) == 2 and all(int(g) >= 150 for _, _, g in finals), finals
+    # the second run resumed (its local step count is what was left, not the whole 150)
+    assert all(int(s) < 150 for _, s, _ in finals), finals
+
+
+@pytest.mark.timeout(300)
 def test_evaluate_cli_scores_a_trained_checkpoint(tmp_path):
     """Train on the CPU tier, then ``python -m ...evaluate``: dropout off, weights or moving averages, same data set."""
     d = str(tmp_path / "ck")

@@ -105,8 +105,40 @@ def test_static_scratch_update_respects_owner_range():
     assert int(s["state"][0].item()) == 930  # bump_global_step = 0 leaves the shared counter alone
 
 
+@pytest.mark.gpu
+def test_static_scratch_update_unaligned_range_and_negative_hi_match_regular_entry_point():
+    """[lo, hi) that cuts 4-element groups, and hi < 0 (= to the end): both entry points must agree."""
+    N, lib, fn = _bind()
+    shapes = [(64, 32), (32, 12)]
+    stream = torch.cuda.current_stream().cuda_stream
+    for lo, hi in ((101, 1703), (7, -1)):
+        a, b = _make_side(N, shapes, seed=8), _make_side(N, shapes, seed=8)
+        grad = torch.randn(a["total"], device="cuda") * 0.1
+        hyper = N.Hyper(0.01, 0.96, 468, 1, 2, 0.01, 0.99, 1, 1.0)
+        peers = N.Peers()
+        peers.n_grads = peers.n_copies = 1
+        peers.grads[0] = grad.data_ptr()
+        rc = lib.ttd_apply_update(a["w"].data_ptr(), a["ema"].data_ptr(), a["table"], a["n"], lo, hi, C.byref(hyper),
+                                  C.byref(peers), a["state"].data_ptr(), 1, stream)
+        assert rc == 0, lib.ttd_last_error()
+        rc = fn(b["w"].data_ptr(), b["ema"].data_ptr(), grad.data_ptr(), b["table"], b["n"], lo, hi, C.byref(hyper),
+                b["state"].data_ptr(), 1, stream)
+        assert rc == 0, lib.ttd_last_error()
+        torch.cuda.synchronize()
+        assert torch.allclose(b["w"], a["w"], rtol=1e-6, atol=1e-7)
+        assert torch.allclose(b["ema"], a["ema"], rtol=1e-6, atol=1e-7)
+        fresh = _make_side(N, shapes, seed=8)["w"]
+        end = a["total"] if hi < 0 else hi
+        last = shapes[-1]
+        used = sum(-(-(r + 1) * c // 64) * 64 for r, c in shapes[:-1]) + (last[0] + 1) * last[1]
+        end = min(end, used)
+        assert (a["w"][lo:end] != fresh[lo:end]).any() and torch.equal(a["w"][:lo], fresh[:lo])
+
+
+@pytest.mark.gpu
 def test_static_scratch_update_refuses_more_groups_than_fit():
-    """Pure host-side check: no GPU is touched when the request exceeds the built-in table."""
+    """Host-side check (no kernel is launched when the request exceeds the built-in table); marked gpu because
+    loading the kernel library needs the CUDA runtime of a GPU box."""
     N, lib, fn = _bind()
     too_many = 65
     table = (N.VarDesc * too_many)()
