@@ -29,7 +29,7 @@ def build_model(input_dim, sizes, act="elu", drop=0.01):
     return nn.Sequential(*layers)
 
 
-def run_ddp_bench(args, rank, world, local_rank) -> int:
+def run_ddp_bench(args, rank, world, local_rank, keep_group: bool = False) -> int:
     device = torch.device("cuda", local_rank)
     if world > 1 and not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -123,7 +123,7 @@ def run_ddp_bench(args, rank, world, local_rank) -> int:
             "e2e": {"value": ex * args.steps / (ms_e2e / 1e3), "unit": "examples/s", "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": B * F * 4 + B * 8, "d2h_bytes_per_step": 4},
         }))
-    if world > 1:
+    if world > 1 and not keep_group:
         dist.barrier(device_ids=[local_rank])
         dist.destroy_process_group()
     return 0

@@ -124,6 +124,62 @@ def reference_arm(args) -> int:
     return 0
 
 
+# BASELINE.md §3 (operative baseline: stock PyTorch + cuBLAS + NCCL on the same box, measured in round 1; the reference
+# itself publishes no number and cannot run here). examples/s of the strongest stock arm per GPU count: the whole-step
+# CUDA graph of PyTorch ops on one GPU, DistributedDataParallel over NCCL beyond.
+BASELINE_MD = {
+    "mnist_sync": {1: 511042.0, 2: 191551.0, 4: 345526.0, 8: 677315.0},
+    "mnist_async": {2: 191551.0, 4: 345526.0, 8: 677315.0},
+}
+
+
+def stock_arm(args, rank, world, local_rank):
+    """The matching stock-PyTorch arm, measured in this same invocation (same box, same steps / warm-up): the
+    whole-step CUDA graph of PyTorch/cuBLAS kernels on one GPU, DDP over NCCL on several. Returns the arm's JSON
+    dict on rank 0 (None elsewhere / when there is no arm for the config)."""
+    import contextlib
+    import io
+    buf = io.StringIO()
+    sub = argparse.Namespace(**vars(args))
+    sub.steps = min(args.steps, 400)  # the eager DDP arm runs ~1.5 ms per step
+    try:
+        with contextlib.redirect_stdout(buf):
+            if world == 1:
+                from baseline.zero1_mlp import run_torch_graph_bench
+                run_torch_graph_bench(sub, rank, world, local_rank)
+            else:
+                from baseline.ddp_mlp import run_ddp_bench
+                run_ddp_bench(sub, rank, world, local_rank, keep_group=True)
+    except Exception as exc:  # noqa: BLE001 - the product's own number must survive a failing baseline arm
+        return {"impl": "stock", "unavailable": f"{type(exc).__name__}: {exc}"} if rank == 0 else None
+    if rank != 0:
+        return None
+    for line in buf.getvalue().splitlines():
+        if line.startswith("{"):
+            try:
+                return json.loads(line)
+            except ValueError:
+                pass
+    return None
+
+
+def replicas_identical(trainer, world) -> bool:
+    """Every replica must hold bit-identical compute copies (what the next forward reads) and the same global_step."""
+    import torch
+    import torch.distributed as dist
+    st = trainer.store
+    parts = [t.view(torch.int16).to(torch.int64).sum() for t in st.w_t if t is not None]
+    parts += [t.view(torch.int16).to(torch.int64).sum() for t in st.w_rm if t is not None]
+    parts += [b.view(torch.int32).to(torch.int64).sum() for b in st.bias_c]
+    parts.append(st.state[0].to(torch.int64))
+    digest = torch.stack(parts)
+    if world == 1:
+        return True
+    all_d = [torch.zeros_like(digest) for _ in range(world)]
+    dist.all_gather(all_d, digest)
+    return all(torch.equal(all_d[0], d) for d in all_d)
+
+
 def run(args) -> int:
     import torch
     import torch.distributed as dist
@@ -160,7 +216,8 @@ def run(args) -> int:
     cfg = TrainConfig(job_name="worker", task_id=rank, worker_hosts=hosts, ps_hosts="127.0.0.1:2221",
                       model=spec["model"], sync_replicas=spec["sync_replicas"], batch_size=args.batch,
                       training_steps=10**9, seed=1234, save_checkpoint_secs=None, cuda_graph=not args.no_graph,
-                      pdl=not args.no_pdl, fused_tail=args.fused_tail, pull_fused=args.pull_fused and not args.no_pull_fused)
+                      pdl=not args.no_pdl, fused_tail=args.fused_tail, pull_fused=args.pull_fused and not args.no_pull_fused,
+                      step_impl=args.step_impl)
     trainer = GpuTrainer(cfg, device_index=local_rank, comm=comm)
     trainer.initialize()
     B, F = cfg.batch_size, cfg.input_dim
@@ -229,6 +286,8 @@ def run(args) -> int:
     ms_e2e = timed(e2e_step, args.steps)
     last = trainer.read_slot(slots[-1])
     sampler.stop()
+    trainer.synchronize()
+    same = replicas_identical(trainer, world) if (cfg.sync_replicas or world == 1) else None
 
     ex_per_step = B * world
     value = ex_per_step * args.steps / (ms / 1e3)
@@ -244,10 +303,13 @@ def run(args) -> int:
             "ms_per_step": ms / args.steps,
             "higher_is_better": True,
             "scaling": "weak",
-            "vs_baseline": None,
+            "vs_baseline": (value / BASELINE_MD[args.config][world]) if world in BASELINE_MD.get(args.config, {}) else None,
+            "vs_baseline_source": "BASELINE.md section 3: strongest stock PyTorch arm on this box measured in round 1 (whole-step "
+                                  "CUDA graph of cuBLAS kernels at 1 GPU, DDP+NCCL at 2/4/8); the reference publishes no number",
             "dtype": "bf16",
             "data": "synthetic MNIST-shaped (28x28x1 float32, 10 classes), random-init weights",
             "impl": "ours",
+            "replicas_identical": same,
             "config": {
                 "model": {"mlp": "distribute_training.py MLP 784-200-100-50-25-10 ELU dropout0.01",
                           "wide_mlp": "wide MLP 784-8192-8192-10", "lenet": "LeNet-5"}[cfg.model],
@@ -270,8 +332,20 @@ def run(args) -> int:
             "final": {"loss": values.loss, "accuracy": values.accuracy, "global_step": values.global_step,
                       "e2e_loss": last.loss, "e2e_global_step": last.global_step},
         }
-        print(json.dumps(out))
     trainer.close()
+    stock = None
+    if args.with_baseline and args.config in ("mnist_sync", "mnist_async", "wide_sync"):
+        stock = stock_arm(args, rank, world, local_rank)  # same process group, after our own timed loops
+    if rank == 0:
+        if stock is not None:
+            if "value" in stock:
+                out["stock_same_run"] = {"impl": stock.get("impl"), "value": stock["value"], "ms_per_step": stock.get("ms_per_step"),
+                                         "e2e_value": (stock.get("e2e") or {}).get("value"), "steps": stock.get("steps"),
+                                         "ratio": value / stock["value"],
+                                         "e2e_ratio": (e2e_value / stock["e2e"]["value"]) if stock.get("e2e") else None}
+            else:
+                out["stock_same_run"] = stock
+        print(json.dumps(out))
     if world > 1:
         dist.barrier(device_ids=[local_rank])
         dist.destroy_process_group()
@@ -292,6 +366,11 @@ def main() -> int:
     ap.add_argument("--pull-fused", action="store_true",
                     help="fetch W1 from its owners inside the first GEMM (K3) instead of the update kernel's broadcast")
     ap.add_argument("--no-pull-fused", action="store_true", help="(default) K3 off")
+    ap.add_argument("--step-impl", default="auto", choices=["auto", "column", "layers"],
+                    help="auto/column: the column kernel where the model fits; layers: one GEMM launch per layer")
+    ap.add_argument("--with-baseline", dest="with_baseline", action="store_true", default=True,
+                    help="(default) also time the matching stock-PyTorch arm in this invocation -> stock_same_run")
+    ap.add_argument("--no-baseline", dest="with_baseline", action="store_false")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

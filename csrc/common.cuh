@@ -20,6 +20,10 @@ int check_cuda(cudaError_t e, const char* what);
     if (_rc != 0) return _rc;                                 \
   } while (0)
 
+// bf16 [rows, ld] matrix with `cols` valid elements per row as a TMA tensor map: box = {64, box_rows}, 128-B swizzle,
+// out-of-bounds elements read as zero (defined in gemm_tcgen05.cu)
+int make_tmap(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows);
+
 // ----------------------------------------------------------------------------------------------
 // generic
 // ----------------------------------------------------------------------------------------------
@@ -172,6 +176,18 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// 32 lanes x 4 consecutive fp32 columns
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float* v) {
+  uint32_t r[4];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(taddr)
+               : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v[i] = __uint_as_float(r[i]);
 }
 
 // UMMA shared-memory operand descriptor: K-major tile, 128-byte swizzle, rows of 64 bf16 (=128 B),

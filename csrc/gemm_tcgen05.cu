@@ -21,6 +21,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "step_state.cuh"
 
 namespace ttd {
 
@@ -54,6 +55,13 @@ struct GemmProblem {
   const long long* labels;
   float* metrics;
   int swap;  // 1: operands were exchanged by the host (rows of the tile = output features, columns = batch)
+  // TTD_EPI_WGRAD_UPDATE: the tile's rows are rows of the variable group [rows+1, cols] (last row = bias)
+  float* upd_w;
+  float* upd_ema;
+  float* upd_bias;
+  int upd_regularize;
+  // A operand taken from a pool of equally shaped matrices stacked along the rows: slot (*step_ptr % a_slots)
+  int a_slot_rows, a_slots;
 };
 
 struct GemmGroup {
@@ -114,6 +122,11 @@ struct EpiCtx {
   uint32_t seed_lo, seed_hi;
   const unsigned long long* step_ptr;
   uint8_t* smem;  // idle pipeline stages, reused as a staging patch by the wgrad epilogue
+  // TTD_EPI_WGRAD_UPDATE (single replica: the optimiser step happens where the gradient is produced)
+  const float* lr_slot = nullptr;  // device float[2]: learning rate and EMA decay of this step
+  float grad_scale = 1.0f, reg_scale = 0.0f;
+  int reg_kind = 0;
+  bool use_ema = false;
 };
 
 // What a forward / dgrad chunk (one row x 16 columns) needs besides the accumulator: bias or saved activation,
@@ -196,6 +209,50 @@ __device__ __forceinline__ void epi_fd_apply(const GemmProblem& P, int m, int n0
   store_row_chunk(P, m, n0, v);
 }
 
+// Master weights and shadow values of one row x 16 columns of a variable group (fused-update epilogue).
+__device__ __forceinline__ void upd_load(const GemmProblem& P, bool use_ema, int m, int n0, bool row_ok, float* w, float* s) {
+#pragma unroll
+  for (int j = 0; j < 16; ++j) w[j] = s[j] = 0.0f;
+  if (!row_ok || n0 >= P.N) return;
+  const bool full = n0 + 16 <= P.N;
+  const float* wr = P.upd_w + static_cast<long long>(m) * P.ldf + n0;
+  if (full && (reinterpret_cast<uintptr_t>(wr) & 15u) == 0) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 t = *reinterpret_cast<const float4*>(wr + 4 * q);
+      w[4 * q] = t.x; w[4 * q + 1] = t.y; w[4 * q + 2] = t.z; w[4 * q + 3] = t.w;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+      if (n0 + j < P.N) w[j] = wr[j];
+  }
+  if (!use_ema) return;
+  const float* sr = P.upd_ema + static_cast<long long>(m) * P.ldf + n0;
+  if (full && (reinterpret_cast<uintptr_t>(sr) & 15u) == 0) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 t = *reinterpret_cast<const float4*>(sr + 4 * q);
+      s[4 * q] = t.x; s[4 * q + 1] = t.y; s[4 * q + 2] = t.z; s[4 * q + 3] = t.w;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+      if (n0 + j < P.N) s[j] = sr[j];
+  }
+}
+__device__ __forceinline__ void store_f32x16(float* dst, const float* v, int n_valid) {
+  if (n_valid >= 16 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      *reinterpret_cast<float4*>(dst + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+      if (j < n_valid) dst[j] = v[j];
+  }
+}
+
 __device__ __forceinline__ void run_epilogue(const GemmProblem& P, const EpiCtx& E, uint32_t tmem_base, int m0,
                                              int nbase, int warp, int lane, uint64_t* acc_bar, uint32_t acc_parity) {
   // ===================== epilogue: TMEM -> registers -> global =====================
@@ -210,6 +267,51 @@ __device__ __forceinline__ void run_epilogue(const GemmProblem& P, const EpiCtx&
   const bool fd = (P.mode == TTD_EPI_FWD || P.mode == TTD_EPI_DGRAD) && !P.swap;
   EpiSide S0, S1;
   if (fd) epi_fd_load(P, E, m, nbase, step, row_ok, S0);
+  if (P.mode == TTD_EPI_WGRAD_UPDATE) {
+    // ===== weight gradient + optimiser step in one epilogue (single replica) ==================================
+    // g = scale*acc*grad_scale (+ L1/L2); w -= lr*g; ema -= (1-d)(ema-w); bf16 copies in both layouts, fp32 bias
+    // copy. Same arithmetic, in the same order, as param_kernel<kUpdate> (reference :150-152, :153-161, :50-55).
+    const int rows = P.M - 1;  // kernel rows; row `rows` of the group is the bias
+    float wv[16], sv[16];
+    upd_load(P, E.use_ema, m, nbase, row_ok, wv, sv);  // master / shadow values: requested before the accumulator is ready
+    const float lr = E.lr_slot[0], ema_d = E.lr_slot[1];
+    mbar_wait(acc_bar, acc_parity);
+    tc_fence_after();
+    for (int c = 0; c < nchunks; ++c) {
+      const int n0 = nbase + c * 16;
+      __syncwarp();
+      tmem_ld16(taddr_row + c * 16, v);
+      float wn[16], sn[16];
+      if (c + 1 < nchunks) upd_load(P, E.use_ema, m, n0 + 16, row_ok, wn, sn);
+      if (row_ok && n0 < P.N) {
+        float val[16], shadow[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          float g = v[j] * P.scale * E.grad_scale;
+          if (P.upd_regularize && m < rows) {
+            if (E.reg_kind == 2) g += E.reg_scale * wv[j];
+            else if (E.reg_kind == 1) g += E.reg_scale * (wv[j] > 0.0f ? 1.0f : (wv[j] < 0.0f ? -1.0f : 0.0f));
+          }
+          val[j] = (n0 + j < P.N) ? wv[j] - lr * g : 0.0f;
+          shadow[j] = sv[j] - (1.0f - ema_d) * (sv[j] - val[j]);
+        }
+        const int n_valid = P.N - n0;
+        store_f32x16(P.upd_w + static_cast<long long>(m) * P.ldf + n0, val, n_valid);
+        if (E.use_ema) store_f32x16(P.upd_ema + static_cast<long long>(m) * P.ldf + n0, shadow, n_valid);
+        if (P.outf != nullptr) {  // the gradient itself, when somebody wants to look at it
+          float gr[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) gr[j] = v[j] * P.scale;
+          store_f32x16(P.outf + static_cast<long long>(m) * P.ldf + n0, gr, n_valid);
+        }
+        if (m < rows) store_row_chunk(P, m, n0, val);  // bf16 compute copies: TF layout (out) and transposed (outT)
+        else if (P.upd_bias != nullptr) store_f32x16(P.upd_bias + n0, val, n_valid);
+      }
+#pragma unroll
+      for (int j = 0; j < 16; ++j) { wv[j] = wn[j]; sv[j] = sn[j]; }
+    }
+    return;
+  }
   mbar_wait(acc_bar, acc_parity);
   tc_fence_after();
 
@@ -610,7 +712,7 @@ static EncodeTiledFn get_encode_fn() {
 
 // bf16 [rows, ld] matrix with `cols` valid elements per row; box = {64, box_rows}, 128-B swizzle,
 // out-of-bounds elements read as zero (this is what pads K=784 / N=200 / M=785 to tile multiples).
-static int make_tmap(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+int make_tmap(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return -2;
   if ((reinterpret_cast<uintptr_t>(base) & 15u) != 0 || (ld % 8) != 0) {
@@ -705,6 +807,10 @@ extern "C" int ttd_gemm_group(const TtdGemmDesc* d, int count, uint64_t seed, co
     }
     if (s.mode == TTD_EPI_WGRAD && s.outf == nullptr) {
       set_error("ttd_gemm_group: wgrad needs outf");
+      return -1;
+    }
+    if (s.mode == TTD_EPI_WGRAD_UPDATE) {
+      set_error("ttd_gemm_group: the fused weight-gradient + update epilogue is served by ttd_gemm_net_launch_ex");
       return -1;
     }
     if (s.mode == TTD_EPI_DGRAD && s.aux == nullptr && (s.act != TTD_ACT_NONE || s.drop_rate > 0.f)) {
@@ -894,6 +1000,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_chain_kernel(const GemmProbl
     P.bias = sP.bias; P.out = sP.out; P.ldo = sP.ldo; P.outT = sP.outT; P.ldt = sP.ldt; P.outf = sP.outf;
     P.ldf = sP.ldf; P.aux = sP.aux; P.ldaux = sP.ldaux; P.scale = sP.scale; P.labels = sP.labels;
     P.metrics = sP.metrics; P.swap = 0;
+    P.upd_w = nullptr; P.upd_ema = nullptr; P.upd_bias = nullptr; P.upd_regularize = 0;
     const CUtensorMap* map_a = &probs[s].tma_a;
     const CUtensorMap* map_b = &probs[s].tma_b;
     const int num_kb = (P.K + kBlockK - 1) / kBlockK;
@@ -980,6 +1087,10 @@ extern "C" int ttd_gemm_chain_build(const TtdGemmDesc* d, int count, void* devic
     }
     if (s.mode == TTD_EPI_FWD_XENT && s.labels == nullptr) {
       set_error("ttd_gemm_chain_build: fused xent needs labels");
+      return -1;
+    }
+    if (s.mode == TTD_EPI_WGRAD_UPDATE) {
+      set_error("ttd_gemm_chain_build: the fused weight-gradient + update epilogue is served by ttd_gemm_net_launch_ex");
       return -1;
     }
     int rc = make_tmap(&P.tma_a, s.a, s.M, s.K, s.lda, kBlockM);
@@ -1082,6 +1193,11 @@ struct NetHeader {
   const unsigned long long* step_ptr;
   int use_pdl;
   unsigned long long* trace;  // optional: per problem (tile 0) {deps met, operands landed, accumulator full, counted in}
+  // fused optimiser step (TTD_EPI_WGRAD_UPDATE problems) and end-of-step bookkeeping by the last CTA to leave
+  TtdHyper hyper;
+  const float* lr_slot;
+  TtdStepState* state;
+  int finalize;               // bit0: the last CTA advances the step state; bit1: ... and global_step
 };
 
 __device__ __forceinline__ unsigned int ld_acquire_gpu_u32(const unsigned int* p) {
@@ -1148,7 +1264,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_net_kernel(const GemmProblem
         if (t.x < 0) break;
         const GemmProblem* P = &probs[t.x];
         const int K = P->K, block_n = P->block_n, tiles_m = P->tiles_m;
-        const int m0 = (t.y % tiles_m) * kBlockM, nbase = (t.y / tiles_m) * block_n;
+        int m0 = (t.y % tiles_m) * kBlockM;
+        const int nbase = (t.y / tiles_m) * block_n;
+        if (P->a_slots > 1 && h.step_ptr != nullptr)  // device-resident data set: this step's batch (rows past M of the
+          m0 += static_cast<int>(*h.step_ptr % static_cast<unsigned long long>(P->a_slots)) * P->a_slot_rows;  // tile are masked)
         // wait for the producers of this problem's operands
         uint32_t mask = h.dep_mask[t.x];
         if (mask != 0) {
@@ -1215,7 +1334,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_net_kernel(const GemmProblem
     }
   } else if (warp >= 4) {
     // ===================== epilogue: TMEM -> registers -> global, then count the tile in =====================
-    const EpiCtx E{h.seed_lo, h.seed_hi, h.step_ptr, patch};
+    EpiCtx E{h.seed_lo, h.seed_hi, h.step_ptr, patch};
+    E.lr_slot = h.lr_slot;
+    E.grad_scale = h.hyper.grad_scale;
+    E.reg_scale = h.hyper.reg_scale;
+    E.reg_kind = h.hyper.reg_kind;
+    E.use_ema = h.hyper.ema_decay > 0.0f;
     uint32_t full_ph[2] = {0, 0};
     int acc = 0;
     for (int j = 0; j < h.max_tasks; ++j) {
@@ -1234,6 +1358,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_net_kernel(const GemmProblem
       P.bias = S.bias; P.out = S.out; P.ldo = S.ldo; P.outT = S.outT; P.ldt = S.ldt; P.outf = S.outf;
       P.ldf = S.ldf; P.aux = S.aux; P.ldaux = S.ldaux; P.scale = S.scale; P.labels = S.labels;
       P.metrics = S.metrics; P.swap = 0;
+      P.upd_w = S.upd_w; P.upd_ema = S.upd_ema; P.upd_bias = S.upd_bias; P.upd_regularize = S.upd_regularize;
       const int m0 = (t.y % P.tiles_m) * kBlockM, nbase = (t.y / P.tiles_m) * P.block_n;
       {
         int met;
@@ -1273,6 +1398,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_net_kernel(const GemmProblem
     if (left == gridDim.x - 1) {
       for (int i = 0; i <= kNetMaxProblems; ++i) h.counters[i] = 0;
       __threadfence();
+      if ((h.finalize & 1) && h.state != nullptr)  // this launch ends the training step
+        finalize_step(h.state, h.hyper, h.lr_slot != nullptr ? h.lr_slot[0] : 0.0f, (h.finalize & 2) != 0);
     }
   }
 }
@@ -1333,6 +1460,10 @@ extern "C" int ttd_gemm_net_build(const TtdGemmDesc* d, int count, const uint32_
       set_error("ttd_gemm_net_build: wgrad needs outf");
       return -1;
     }
+    if (s.mode == TTD_EPI_WGRAD_UPDATE && (s.upd_w == nullptr || s.ldf < s.N)) {
+      set_error("ttd_gemm_net_build: the fused update needs the master weights and their row pitch (ldf >= N)");
+      return -1;
+    }
     const int n16 = ((s.N + 15) / 16) * 16;
     bn[i] = s.mode == TTD_EPI_FWD_XENT ? n16 : (s.mode == TTD_EPI_WGRAD ? 32 : 16);
     if (bn[i] > 256) bn[i] = 256;
@@ -1371,10 +1502,12 @@ extern "C" int ttd_gemm_net_build(const TtdGemmDesc* d, int count, const uint32_
   for (int i = 0; i < count; ++i) {
     const TtdGemmDesc& s = d[i];
     GemmProblem& P = probs[i];
-    int rc = make_tmap(&P.tma_a, s.a, s.M, s.K, s.lda, kBlockM);
+    const int64_t a_rows = s.a_slots > 1 ? static_cast<int64_t>(s.a_slots) * s.a_slot_rows : s.M;
+    int rc = make_tmap(&P.tma_a, s.a, a_rows, s.K, s.lda, kBlockM);
     if (rc) return rc;
     rc = make_tmap(&P.tma_b, s.b, s.N, s.K, s.ldb, bn[i]);
     if (rc) return rc;
+    P.a_slot_rows = s.a_slot_rows; P.a_slots = s.a_slots;
     P.M = s.M; P.N = s.N; P.K = s.K;
     P.block_n = bn[i];
     P.tiles_m = tiles_m[i];
@@ -1390,6 +1523,7 @@ extern "C" int ttd_gemm_net_build(const TtdGemmDesc* d, int count, const uint32_
     P.labels = reinterpret_cast<const long long*>(s.labels);
     P.metrics = s.metrics;
     P.swap = 0;
+    P.upd_w = s.upd_w; P.upd_ema = s.upd_ema; P.upd_bias = s.upd_bias; P.upd_regularize = s.upd_regularize;
     for (int t = 0; t < tiles[i]; ++t, ++g) tasks[(g % ctas) * max_tasks + g / ctas] = make_int2(i, t);
   }
   memcpy(host.data() + L.dep, dep_mask, sizeof(uint32_t) * count);
@@ -1403,9 +1537,16 @@ static unsigned long long* g_net_trace = nullptr;
 // Diagnostic: device buffer of 4 x n_problems uint64 timestamps (NULL switches it off).
 extern "C" void ttd_gemm_net_set_trace(void* device_buf) { g_net_trace = static_cast<unsigned long long*>(device_buf); }
 
-// `ctas` is what ttd_gemm_net_build returned; grid / max_tasks the values it was built with.
 extern "C" int ttd_gemm_net_launch(const void* device_buf, int count, int grid, int max_tasks, int ctas, uint64_t seed,
                                    const uint64_t* step_ptr, uint32_t flags, void* stream) {
+  return ttd_gemm_net_launch_ex(device_buf, count, grid, max_tasks, ctas, seed, step_ptr, flags, nullptr, nullptr, nullptr,
+                                0, stream);
+}
+
+// `ctas` is what ttd_gemm_net_build returned; grid / max_tasks the values it was built with.
+extern "C" int ttd_gemm_net_launch_ex(const void* device_buf, int count, int grid, int max_tasks, int ctas, uint64_t seed,
+                                      const uint64_t* step_ptr, uint32_t flags, const TtdHyper* hyper,
+                                      const float* lr_slot, TtdStepState* state, int32_t finalize, void* stream) {
   if (count < 1 || count > kNetMaxProblems || ctas < 1 || ctas > grid) {
     set_error("ttd_gemm_net_launch: bad problem / CTA count (%d, %d of %d)", count, ctas, grid);
     return -1;
@@ -1438,6 +1579,10 @@ extern "C" int ttd_gemm_net_launch(const void* device_buf, int count, int grid, 
   h.step_ptr = reinterpret_cast<const unsigned long long*>(step_ptr);
   h.use_pdl = (flags & 1u) ? 1 : 0;
   h.trace = g_net_trace;
+  if (hyper != nullptr) h.hyper = *hyper;
+  h.lr_slot = lr_slot;
+  h.state = state;
+  h.finalize = finalize;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(ctas);

@@ -45,6 +45,12 @@ struct Feeder {
   cudaEvent_t ready[2] = {nullptr, nullptr};  // batch in slot i has landed        (recorded on copy)
   cudaEvent_t freed[2] = {nullptr, nullptr};  // last step that read slot i is done (recorded on compute)
   int pending = -1;                           // slot fed for the next step, -1: none
+  // optional conversion of a freshly copied slot (fp32 rows -> bf16 rows + transposed bf16 rows) on the copy
+  // stream, so that the step's first kernel finds its operands ready instead of converting on the critical path
+  int prep_B = 0, prep_F = 0;
+  __nv_bfloat16* prep_xb = nullptr;
+  __nv_bfloat16* prep_xT = nullptr;
+  long long prep_ldx = 0, prep_ldt = 0;
 };
 }  // namespace ttd
 
@@ -86,6 +92,17 @@ extern "C" void ttd_feeder_destroy(void* h) {
   delete f;
 }
 
+// Slot s is converted right after its copy: xb + s*B*ldx receives the bf16 rows [B, ldx], xT + s*(F+1)*ldt the
+// transposed rows [F, ldt] (row F of every slot is the caller's ones row). NULL xb switches the conversion off.
+extern "C" int ttd_feeder_set_prep(void* h, int32_t B, int32_t F, void* xb, int64_t ldx, void* xT, int64_t ldt) {
+  auto* f = static_cast<ttd::Feeder*>(h);
+  if (f == nullptr) return -1;
+  f->prep_B = B; f->prep_F = F;
+  f->prep_xb = static_cast<__nv_bfloat16*>(xb); f->prep_ldx = ldx;
+  f->prep_xT = static_cast<__nv_bfloat16*>(xT); f->prep_ldt = ldt;
+  return 0;
+}
+
 // H2D of the batch for step `step` (slot step & 1) on the copy stream, behind the last reader of that slot.
 extern "C" int ttd_feeder_feed(void* h, const void* host_x, const void* host_y, uint64_t step) {
   auto* f = static_cast<ttd::Feeder*>(h);
@@ -93,6 +110,13 @@ extern "C" int ttd_feeder_feed(void* h, const void* host_x, const void* host_y, 
   TTD_RT(cudaStreamWaitEvent(f->copy, f->freed[s], 0));
   TTD_RT(cudaMemcpyAsync(f->x_slot[s], host_x, f->x_bytes, cudaMemcpyHostToDevice, f->copy));
   TTD_RT(cudaMemcpyAsync(f->y_slot[s], host_y, f->y_bytes, cudaMemcpyHostToDevice, f->copy));
+  if (f->prep_xb != nullptr) {
+    const int B = f->prep_B, F = f->prep_F;
+    if (ttd_prep_input_ex(static_cast<const float*>(f->x_slot[s]), B, F, f->prep_xb + static_cast<long long>(s) * B * f->prep_ldx,
+                          f->prep_ldx, f->prep_xT + static_cast<long long>(s) * (F + 1) * f->prep_ldt, f->prep_ldt, nullptr,
+                          nullptr, 1, nullptr, nullptr, 0, f->copy) != 0)
+      return -1;
+  }
   TTD_RT(cudaEventRecord(f->ready[s], f->copy));
   f->pending = s;
   return 0;

@@ -34,6 +34,7 @@
 
 #include "../include/ttd_b200.h"
 #include "common.cuh"
+#include "step_state.cuh"
 
 namespace ttd {
 
@@ -137,29 +138,7 @@ __global__ void __launch_bounds__(256) update_static_kernel(unsigned char* __res
   __syncthreads();
   if (s_last && threadIdx.x == 0) {
     *done = 0;
-    if (bump_global_step) st->global_step += 1;
-    st->local_step += 1;
-    st->lr_last = lr;
-    st->metrics_out[0] = st->metrics_acc[0];
-    st->metrics_out[1] = st->metrics_acc[1];
-    st->metrics_acc[0] = 0.0f;
-    st->metrics_acc[1] = 0.0f;
-    __threadfence();
-    if (h.host_mirror != nullptr && h.mirror_slots > 0) {
-      // same pinned-ring mirror as the regular kernel (tagged 16-byte chunks, see param_store.cu)
-      const uint4* src = reinterpret_cast<const uint4*>(st);
-      uint4* dst = reinterpret_cast<uint4*>(static_cast<TtdStepState*>(h.host_mirror) +
-                                            (st->local_step - 1) % static_cast<uint64_t>(h.mirror_slots));
-      const uint32_t tag = static_cast<uint32_t>(st->local_step);
-      uint4 c1 = src[1], c2 = src[2], c3 = src[3];
-      c1.x = tag;
-      c2.x = tag;
-      c3.w = tag;
-      dst[1] = c1;
-      dst[2] = c2;
-      dst[3] = c3;
-      dst[0] = src[0];
-    }
+    finalize_step(st, h, lr, bump_global_step != 0);  // counters, metrics, pinned host mirror: as the regular kernel
   }
 }
 

@@ -30,7 +30,11 @@ enum {
   TTD_EPI_FWD = 0,      /* out = dropout(act(acc + bias))            (reference :54-58) */
   TTD_EPI_DGRAD = 1,    /* out = acc * dropout_mask/keep * act'(aux) (autodiff of :54-58) */
   TTD_EPI_WGRAD = 2,    /* outf = scale * acc, fp32                  (autodiff of :54-55) */
-  TTD_EPI_FWD_XENT = 3  /* logits = acc + bias; mean sparse softmax CE + top-1 + dlogits (reference :77-82, :96, :125) */
+  TTD_EPI_FWD_XENT = 3, /* logits = acc + bias; mean sparse softmax CE + top-1 + dlogits (reference :77-82, :96, :125) */
+  TTD_EPI_WGRAD_UPDATE = 4 /* single replica: weight gradient AND the optimiser step of that variable group in one
+                              epilogue — SGD + L1/L2 + EMA on the fp32 master/shadow, bf16 compute copies (`out` = TF
+                              layout, `outT` = transposed) and the fp32 bias copy (reference :150-152, :153-161). Net
+                              kernel only (ttd_gemm_net_launch_ex carries the hyper-parameters). */
 };
 enum { TTD_ACT_NONE = 0, TTD_ACT_RELU = 1, TTD_ACT_ELU = 2 };
 
@@ -60,6 +64,14 @@ typedef struct TtdGemmDesc {
   const void* b_peer[8];
   int32_t k_bound[9];
   int32_t n_b_peers;            /* 0 = B is read locally */
+  /* TTD_EPI_WGRAD_UPDATE: the problem's [M, N] result is the gradient of the variable group [rows+1, cols] */
+  int32_t upd_regularize;       /* 1: kernel rows take the L1/L2 term */
+  float* upd_w;                 /* fp32 master [M, ldf] (ldf = row pitch of the group in the flat buffer = N) */
+  float* upd_ema;               /* fp32 shadow [M, ldf] or NULL */
+  float* upd_bias;              /* fp32 [N] compute copy of the bias row or NULL */
+  /* Net kernel: A taken from a pool of a_slots matrices of a_slot_rows rows each, stacked along the rows (the
+   * transposed batches of a device-resident data set): slot (*step_ptr % a_slots) is read. 0 / 1 = plain A. */
+  int32_t a_slot_rows, a_slots;
 } TtdGemmDesc;
 
 /* Launch up to 4 independent GEMM problems in ONE kernel (grid = sum of their tiles).
@@ -234,6 +246,49 @@ typedef struct TtdTailDesc {
 /* flags bit0: programmatic dependent launch */
 int ttd_mlp_tail(const TtdTailDesc* desc_host, uint64_t seed, uint32_t flags, void* stream);
 
+/* ---- column kernel: forward + loss + data gradients of a narrow MLP in ONE launch ------------------------- */
+/* The batch is cut into slices of 16 examples; one CTA owns a slice through every layer. Weights are the
+ * 128-row tcgen05 operand (layers behind the first stay resident in shared memory, the first layer's are streamed
+ * once per cluster by TMA multicast), the slice's activations are the 16-column operand and never leave shared
+ * memory between layers: an epilogue writes the next layer's swizzled K-major operand in place. Outputs are the
+ * transposed activations / pre-activation gradients the weight-gradient GEMMs read (row `out` of aT is the caller's
+ * ones row). Dropout masks use the same Philox stream as the per-layer GEMM epilogues (seed, step, layer, row, col).
+ * Limits: <= TTD_COL_MAX_LAYERS layers, hidden widths <= 256, <= 32 classes, operands must fit 227 KB.
+ * Reference semantics: :54-61 (layers), :80-82 (loss), :96/:125 (accuracy), :152 (gradients). */
+#define TTD_COL_MAX_LAYERS 6
+typedef struct TtdColumnLayer {
+  int32_t in, out;
+  uint32_t layer_id;            /* dropout RNG stream of this layer's output */
+  int32_t reserved;
+  const void* w_t;  int64_t ld_t;   /* bf16 [out, ld_t]: transposed compute copy (forward operand) */
+  const void* w_rm; int64_t ld_rm;  /* bf16 [in, ld_rm]: TF-layout compute copy (data-gradient operand); unused for layer 0 */
+  const float* bias;                /* fp32 [out] */
+  void* aT;  int64_t ld_aT;         /* out: bf16 [out(+1), ld_aT] post-dropout activation, transposed (hidden layers) */
+  void* dzT; int64_t ld_dzT;        /* out: bf16 [out, ld_dzT] gradient w.r.t. the pre-activation, transposed */
+} TtdColumnLayer;
+typedef struct TtdColumnDesc {
+  int32_t B, n_layers;
+  int32_t act;                  /* TTD_ACT_* of the hidden layers */
+  float drop_rate;              /* dropout on every hidden layer's output */
+  int32_t cluster;              /* CTAs sharing the first layer's weight stream: 0 = largest of 8/4/2/1 that divides ceil(B/16) */
+  int32_t pool_batches;         /* batches in x_pool / labels_pool; batch (*step_ptr % pool_batches) is used */
+  const void* x_pool; int64_t ld_x;   /* bf16 [pool_batches * B, ld_x] input rows */
+  const int64_t* labels_pool;         /* int64 [pool_batches * B] */
+  float* metrics;                     /* float[2]: += mean loss, += accuracy */
+  const uint64_t* step_ptr;           /* device: local step (dropout RNG, pool slot) */
+  const int64_t* global_step_ptr;     /* device: global step for the learning-rate schedule, or NULL */
+  float* lr_out;                      /* device float[2]: this step's learning rate and EMA decay (NULL: not computed) */
+  TtdHyper hyper;                     /* schedule constants for lr_out */
+  TtdColumnLayer layer[TTD_COL_MAX_LAYERS];
+} TtdColumnDesc;
+/* Plans shared memory / TMEM and encodes the tensor maps once; returns an opaque handle (NULL + error on failure). */
+void* ttd_mlp_column_create(const TtdColumnDesc* desc_host);
+void ttd_mlp_column_destroy(void* handle);
+/* flags bit0: programmatic dependent launch. */
+int ttd_mlp_column_launch(void* handle, uint64_t seed, uint32_t flags, void* stream);
+/* 1 if a model of these sizes fits the kernel (hidden widths, class count, shared memory), else 0. */
+int ttd_mlp_column_fits(int32_t input_dim, const int32_t* layer_sizes, int32_t n_layers);
+
 /* ---- LeNet-5 convolution stages (BASELINE config 5; the reference itself has no CNN) --------------------- */
 /* One stage = conv KHxKW stride 1 (SAME or VALID) + bias + activation + 2x2 max-pool, NHWC fp32 activations.
  * Weights: bf16 [KH*KW*Cin, ldw] (the store's TF-layout compute copy of the HWIO kernel), bias fp32 [Cout]. */
@@ -266,6 +321,13 @@ int ttd_gemm_net_build(const TtdGemmDesc* descs, int count, const uint32_t* dep_
                        void* device_buf, void* stream);
 int ttd_gemm_net_launch(const void* device_buf, int count, int grid, int max_tasks, int ctas, uint64_t seed,
                         const uint64_t* step_ptr, uint32_t flags, void* stream);
+/* Same launch with the optimiser state for TTD_EPI_WGRAD_UPDATE problems: hyper (regulariser, grad_scale, EMA on/off,
+ * host mirror), lr_slot = device float[2] {learning rate, EMA decay} of this step (written by the column kernel),
+ * and — finalize bit0 — the last CTA to leave ends the step: ++local_step, metrics_out <- metrics_acc <- 0, host
+ * mirror; bit1: ++global_step as well (reference :152). */
+int ttd_gemm_net_launch_ex(const void* device_buf, int count, int grid, int max_tasks, int ctas, uint64_t seed,
+                           const uint64_t* step_ptr, uint32_t flags, const TtdHyper* hyper_host, const float* lr_slot,
+                           TtdStepState* state, int32_t finalize, void* stream);
 void ttd_gemm_net_set_trace(void* device_buf_4_u64_per_problem);
 
 /* ---- step feeder: the host side of a training step in one native call (reference: the C++ session run loop
@@ -275,6 +337,9 @@ void ttd_gemm_net_set_trace(void* device_buf_4_u64_per_problem);
 void* ttd_feeder_create(void* compute_stream, void* copy_stream, void* x_slot0, void* x_slot1, void* y_slot0,
                         void* y_slot1, size_t x_bytes, size_t y_bytes);
 void ttd_feeder_destroy(void* feeder);
+/* Convert every fed slot on the copy stream (fp32 [B,F] -> bf16 rows at xb + slot*B*ldx and transposed bf16 rows at
+ * xT + slot*(F+1)*ldt): the input staging leaves the step's critical path. xb = NULL switches it off. */
+int ttd_feeder_set_prep(void* feeder, int32_t B, int32_t F, void* xb, int64_t ldx, void* xT, int64_t ldt);
 int ttd_feeder_feed(void* feeder, const void* host_x, const void* host_y, uint64_t step);
 int ttd_feeder_before_step(void* feeder); /* returns the fed slot or -1; < -1 never; -1 with an error set on failure */
 int ttd_feeder_after_step(void* feeder);

@@ -94,6 +94,10 @@ class TrainConfig:
     prefetch_impl: str = "native"  # native: C++ threads filling a pinned ring (csrc/io/loader.cc) | python: queue.Queue
     cuda_graph: bool = True
     pdl: bool = True  # programmatic dependent launch between the kernels of a step
+    step_impl: str = "auto"  # auto | column | layers. column: forward + loss + data gradients of a narrow MLP as ONE
+    # launch with the activations resident in shared memory (mlp_column_kernel), then every weight gradient — and, with
+    # one replica, the optimiser step — as a second launch; the default wherever the model fits. layers: one tcgen05
+    # GEMM launch per layer (what wide layers and LeNet's dense head use).
     fused_tail: bool = False  # narrow layers behind the first in ONE launch (measured slower than a launch per
     # layer on B200: one CTA serialises epilogues that separate launches spread over several CTAs; see profiles/)
     tail_impl: str = "chain"  # chain: single-CTA tcgen05 chain kernel | cluster: fp32 CUDA-core cluster kernel |
@@ -168,6 +172,8 @@ class TrainConfig:
             raise ValueError(f"--activation must be elu|relu|none, got {self.activation!r}")
         if self.regularizer not in ("none", "l1", "l2"):
             raise ValueError(f"--regularizer must be none|l1|l2, got {self.regularizer!r}")
+        if self.step_impl not in ("auto", "column", "layers"):
+            raise ValueError(f"--step_impl must be auto|column|layers, got {self.step_impl!r}")
         if self.model not in ("mlp", "wide_mlp", "lenet"):
             raise ValueError(f"--model must be mlp|wide_mlp|lenet, got {self.model!r}")
         if not 0.0 <= self.dropout_rate < 1.0:

@@ -35,6 +35,11 @@ TAIL_MAX_WIDTH = 256   # layers wider than this go through the tcgen05 GEMM, not
 TAIL_MAX_BATCH = 256
 
 
+def chain_forced(chain) -> bool:
+    """``chain="force"`` keeps the single-CTA chain kernel although the column kernel would apply (tests, A/B runs)."""
+    return chain == "force"
+
+
 def chain_eligible(sizes: Sequence[int], batch: int) -> bool:
     """sizes = [n_0 .. n_L]: every layer behind the first must fit one tcgen05 tile per GEMM (K, N <= 256)."""
     return len(sizes) >= 3 and batch <= 256 and max(sizes[1:]) <= 256 and 3 * (len(sizes) - 2) <= 32
@@ -54,7 +59,8 @@ def tail_groups(layer_sizes: Sequence[int], batch: int, first_group: int = 0, en
 class GpuMlp:
     def __init__(self, store: GpuParamStore, batch: int, *, activation: str = "elu", dropout_rate: float = 0.01,
                  seed: int = 0, pdl: bool = False, keep_logits: bool = False, first_group: int = 0,
-                 feed_input: bool = True, input_grad: bool = False, chain: bool = True, net: bool = False):
+                 feed_input: bool = True, input_grad: bool = False, chain: bool = True, net: bool = False,
+                 column: bool = True):
         """``first_group`` > 0 makes this the dense head of a larger model (LeNet): its input activations
         ``a[0]`` / ``aT[0]`` are then written by the stage in front (``feed_input=False``) and, with
         ``input_grad``, the backward pass also produces ``dz0`` = dL/d(input) * act'(input) for that stage."""
@@ -93,6 +99,21 @@ class GpuMlp:
         self.use_net = bool(net) and not self.use_tail and not (store.pull_fused_first and first_group == 0)
         if self.use_net:
             self.use_chain = False
+        # column: forward + loss + data gradients as ONE launch with the activations resident in shared memory
+        # (mlp_column_kernel), then every weight gradient as one launch (net kernel) — with one replica the
+        # optimiser step rides in that launch's epilogue. The default for narrow stacks.
+        self.use_column = bool(column and first_group == 0 and feed_input and not input_grad and self.L >= 2
+                               and not self.use_tail and not self.use_net and not chain_forced(chain)
+                               and not store.pull_fused_first and gemm.column_fits(sizes[0], sizes[1:]))
+        self.fused_update = self.use_column and store.world == 1
+        self._column: Optional[gemm.MlpColumn] = None
+        self._wnet: Optional[gemm.GemmNet] = None
+        self._wnet_grads: Optional[gemm.GemmNet] = None
+        self._pool_static = False
+        self.x16: Optional[torch.Tensor] = None   # bf16 [P*B, ld0]      input rows of every pool slot
+        self.xT16: Optional[torch.Tensor] = None  # bf16 [P*(F+1), ldB]  the same, transposed, ones row last
+        if self.use_column:
+            self.use_chain = False
         self._build_descs()
         if self.use_net:
             self._build_net()
@@ -111,6 +132,86 @@ class GpuMlp:
             assert x_pool.dim() == 3 and tuple(x_pool.shape[1:]) == tuple(self.x.shape) and x_pool.is_contiguous()
             assert labels_pool is not None and tuple(labels_pool.shape) == tuple(x_pool.shape[:2])
         self.x_pool, self.labels_pool = x_pool, labels_pool
+        if self.use_column:
+            self._build_column(static=x_pool is not None)
+
+    # -------------------------------------------------------------------------------------------
+    def set_feed_pool(self, feed_x: torch.Tensor, feed_y: torch.Tensor):
+        """Host-fed batches: ``feed_x`` [S, B, F] fp32 / ``feed_y`` [S, B] are staging slots filled by H2D copies.
+        Column mode: whoever fills slot s must also convert it (``prep_slot`` / the native feeder's prep hook) —
+        the conversion then runs on the copy stream, off the step's critical path. Returns the conversion
+        targets (x16, ld, xT16, ld) or None when the model converts inside the step."""
+        self.x_pool, self.labels_pool = feed_x, feed_y
+        if not self.use_column:
+            return None
+        self._build_column(static=False)
+        return self.x16, self.x16.stride(0), self.xT16, self.xT16.stride(0)
+
+    def prep_slot(self, slot: int) -> None:
+        """fp32 slot -> bf16 rows + transposed rows of the same slot (column mode), on the current stream."""
+        B, F = self.B, self.sizes[0]
+        src = self.x_pool[slot] if self.x_pool is not None else self.x
+        gemm.prep_input(src, self.x16[slot * B:(slot + 1) * B], self.xT16[slot * (F + 1):slot * (F + 1) + F])
+
+    def _build_column(self, static: bool) -> None:
+        s, B, sz = self.store, self.B, self.sizes
+        dev = s.device
+        F, ldB = sz[0], _pad8(B)
+        P = int(self.x_pool.shape[0]) if self.x_pool is not None else 1
+        self._pool_static = static
+        if self._column is not None:
+            self._column.close()
+        self.x16 = torch.zeros(P * B, _pad8(F), device=dev, dtype=torch.bfloat16)
+        self.xT16 = torch.zeros(P * (F + 1), ldB, device=dev, dtype=torch.bfloat16)
+        self.xT16.view(P, F + 1, ldB)[:, F, :B] = 1.0  # ones row: the bias gradient falls out of the wgrad GEMM
+        if static:  # a device-resident data set is converted once, here
+            for slot in range(P):
+                self.prep_slot(slot)
+        d = N.ColumnDesc()
+        d.B, d.n_layers, d.act, d.drop_rate = B, self.L, self.act, self.drop
+        d.cluster, d.pool_batches = 0, P
+        d.x_pool, d.ld_x = self.x16.data_ptr(), self.x16.stride(0)
+        labels = self.labels_pool if self.labels_pool is not None else self.labels
+        d.labels_pool = labels.data_ptr()
+        d.metrics = s.metrics_acc_ptr
+        d.step_ptr = s.local_step_ptr
+        d.global_step_ptr = s.global_step_ptr
+        d.lr_out = s.lr_slot.data_ptr()
+        d.hyper = s.hyper_native
+        for l in range(1, self.L + 1):
+            y = d.layer[l - 1]
+            gi = self.g0 + l - 1
+            y.in_, y.out, y.layer_id = sz[l - 1], sz[l], l
+            y.w_t, y.ld_t = s.w_t[gi].data_ptr(), s.w_t[gi].stride(0)
+            if l >= 2:
+                y.w_rm, y.ld_rm = s.w_rm[gi].data_ptr(), s.w_rm[gi].stride(0)
+            y.bias = s.bias(gi).data_ptr()
+            if l < self.L:
+                y.aT, y.ld_aT = self.aT[l].data_ptr(), self.aT[l].stride(0)
+            y.dzT, y.ld_dzT = self.dzT[l - 1].data_ptr(), self.dzT[l - 1].stride(0)
+        self._column = gemm.MlpColumn(d)
+        # every weight gradient in ONE launch; with a single replica the update happens in its epilogue
+        self._wnet = self._build_wnet(fused=self.fused_update)
+        self._wnet_grads = None if self.fused_update else self._wnet  # plain gradients: built on first use
+
+    def _build_wnet(self, fused: bool) -> "gemm.GemmNet":
+        s, B, sz = self.store, self.B, self.sizes
+        F = sz[0]
+        P = self.xT16.shape[0] // (F + 1)
+        descs = []
+        for l in range(self.L, 0, -1):
+            gi = self.g0 + l - 1
+            a = self.aT[l - 1] if l >= 2 else self.xT16
+            kw = dict(a_slot_rows=F + 1, a_slots=P) if l == 1 else {}
+            if fused:
+                descs.append(gemm.make_desc(a, self.dzT[l - 1], sz[l - 1] + 1, sz[l], B, N.EPI_WGRAD_UPDATE, scale=1.0,
+                                            out=s.w_rm[gi], outT=s.w_t[gi], upd_w=s.master_matrix(gi),
+                                            upd_ema=s.ema_matrix(gi) if s.hyper.ema_decay > 0 else None,
+                                            upd_bias=s.bias(gi), upd_regularize=s.layout.groups[gi].regularize, **kw))
+            else:
+                descs.append(gemm.make_desc(a, self.dzT[l - 1], sz[l - 1] + 1, sz[l], B, N.EPI_WGRAD,
+                                            outf=s.grad_matrix(gi), scale=1.0, **kw))
+        return gemm.GemmNet(descs, [[] for _ in descs], s.device)
 
     # -------------------------------------------------------------------------------------------
     def _build_descs(self) -> None:
@@ -216,6 +317,13 @@ class GpuMlp:
         """Enqueue forward + backward on the current stream; returns the number of kernels launched."""
         step_ptr = self.store.local_step_ptr
         n = 0
+        if self.use_column:
+            if self._column is None:
+                self._build_column(static=False)
+            if self.x_pool is None:  # single fed batch: converted inside the step
+                self.prep_slot(0)
+                n += 1
+            return n + self.launch_forward() + self.launch_backward()
         if not self.feed_input:
             pass
         elif self.x_pool is not None:
@@ -228,6 +336,9 @@ class GpuMlp:
 
     def launch_forward(self) -> int:
         step_ptr, n = self.store.local_step_ptr, 0
+        if self.use_column:  # forward, loss and every data gradient: one launch
+            self._column.launch(seed=self.seed, pdl=self.pdl)
+            return 1
         if self.use_net:  # forward, loss and the whole backward: one launch
             self._net.launch(seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
             return 1
@@ -243,8 +354,21 @@ class GpuMlp:
             n += 1
         return n
 
-    def launch_backward(self) -> int:
+    def launch_backward(self, update: bool = False, bump_global_step: bool = True) -> int:
+        """Weight gradients (and what is left of the data gradients). ``update`` (column mode, one replica): the
+        optimiser step and the end-of-step bookkeeping ride in the same launch."""
         step_ptr, n = self.store.local_step_ptr, 0
+        if self.use_column:
+            s = self.store
+            if update and self.fused_update:
+                self._wnet.launch(seed=self.seed, step_ptr=step_ptr, pdl=self.pdl, hyper=s.hyper_native,
+                                  lr_slot=s.lr_slot.data_ptr(), state_ptr=s.state_ptr,
+                                  finalize=1 | (2 if bump_global_step else 0))
+            else:  # plain gradients into the flat buffer (several replicas, async mode, gradient checks)
+                if self._wnet_grads is None:
+                    self._wnet_grads = self._build_wnet(fused=False)
+                self._wnet_grads.launch(seed=self.seed, step_ptr=step_ptr, pdl=self.pdl)
+            return 1
         if self.use_net:
             return 0
         if self.use_tail or self.use_chain:  # dz of the first layer and every other gradient exist already
@@ -257,6 +381,14 @@ class GpuMlp:
 
     def launch_step(self, bump_global_step: bool = True, sync: bool = True) -> int:
         """sync: fwd/bwd + the fused push (aggregate of all replicas). async: pull + fwd/bwd + atomic push."""
+        if sync and self.use_column and self.fused_update:
+            if self._column is None:
+                self._build_column(static=False)
+            n = 0
+            if self.x_pool is None:
+                self.prep_slot(0)
+                n = 1
+            return n + self.launch_forward() + self.launch_backward(update=True, bump_global_step=bump_global_step)
         if sync:
             n = self.launch_forward_backward()
             self.store.apply_update(bump_global_step, pdl=self.pdl)

@@ -15,7 +15,7 @@ from .. import _build
 
 MAX_PEERS = 8
 
-EPI_FWD, EPI_DGRAD, EPI_WGRAD, EPI_FWD_XENT = 0, 1, 2, 3
+EPI_FWD, EPI_DGRAD, EPI_WGRAD, EPI_FWD_XENT, EPI_WGRAD_UPDATE = 0, 1, 2, 3, 4
 ACT_NONE, ACT_RELU, ACT_ELU = 0, 1, 2
 ACT_CODES = {"none": ACT_NONE, "relu": ACT_RELU, "elu": ACT_ELU}
 REG_CODES = {"none": 0, "l1": 1, "l2": 2}
@@ -42,6 +42,11 @@ class GemmDesc(C.Structure):
         ("b_peer", C.c_void_p * 8),
         ("k_bound", C.c_int32 * 9),
         ("n_b_peers", C.c_int32),
+        ("upd_regularize", C.c_int32),
+        ("upd_w", C.c_void_p),
+        ("upd_ema", C.c_void_p),
+        ("upd_bias", C.c_void_p),
+        ("a_slot_rows", C.c_int32), ("a_slots", C.c_int32),
     ]
 
 
@@ -150,6 +155,30 @@ class TailDesc(C.Structure):
     ]
 
 
+COL_MAX_LAYERS = 6
+
+
+class ColumnLayer(C.Structure):
+    _fields_ = [
+        ("in_", C.c_int32), ("out", C.c_int32), ("layer_id", C.c_uint32), ("reserved", C.c_int32),
+        ("w_t", C.c_void_p), ("ld_t", C.c_int64), ("w_rm", C.c_void_p), ("ld_rm", C.c_int64),
+        ("bias", C.c_void_p),
+        ("aT", C.c_void_p), ("ld_aT", C.c_int64), ("dzT", C.c_void_p), ("ld_dzT", C.c_int64),
+    ]
+
+
+class ColumnDesc(C.Structure):
+    _fields_ = [
+        ("B", C.c_int32), ("n_layers", C.c_int32), ("act", C.c_int32), ("drop_rate", C.c_float),
+        ("cluster", C.c_int32), ("pool_batches", C.c_int32),
+        ("x_pool", C.c_void_p), ("ld_x", C.c_int64),
+        ("labels_pool", C.c_void_p), ("metrics", C.c_void_p), ("step_ptr", C.c_void_p),
+        ("global_step_ptr", C.c_void_p), ("lr_out", C.c_void_p),
+        ("hyper", Hyper),
+        ("layer", ColumnLayer * COL_MAX_LAYERS),
+    ]
+
+
 class NativeError(RuntimeError):
     pass
 
@@ -194,6 +223,17 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.ttd_gemm_net_launch.restype = C.c_int
     lib.ttd_gemm_net_launch.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_uint32,
                                         C.c_void_p]
+    lib.ttd_gemm_net_launch_ex.restype = C.c_int
+    lib.ttd_gemm_net_launch_ex.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_void_p,
+                                           C.c_uint32, C.POINTER(Hyper), C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
+    lib.ttd_mlp_column_create.restype = C.c_void_p
+    lib.ttd_mlp_column_create.argtypes = [C.POINTER(ColumnDesc)]
+    lib.ttd_mlp_column_destroy.restype = None
+    lib.ttd_mlp_column_destroy.argtypes = [C.c_void_p]
+    lib.ttd_mlp_column_launch.restype = C.c_int
+    lib.ttd_mlp_column_launch.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p]
+    lib.ttd_mlp_column_fits.restype = C.c_int
+    lib.ttd_mlp_column_fits.argtypes = [C.c_int32, C.POINTER(C.c_int32), C.c_int32]
     lib.ttd_gemm_net_set_trace.restype = None
     lib.ttd_gemm_net_set_trace.argtypes = [C.c_void_p]
     lib.ttd_softmax_xent.restype = C.c_int
@@ -209,6 +249,8 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.ttd_feeder_create.argtypes = [C.c_void_p] * 6 + [C.c_size_t, C.c_size_t]
     lib.ttd_feeder_destroy.restype = None
     lib.ttd_feeder_destroy.argtypes = [C.c_void_p]
+    lib.ttd_feeder_set_prep.restype = C.c_int
+    lib.ttd_feeder_set_prep.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
     lib.ttd_feeder_feed.restype = C.c_int
     lib.ttd_feeder_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
     lib.ttd_feeder_before_step.restype = C.c_int

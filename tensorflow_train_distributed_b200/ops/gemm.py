@@ -31,7 +31,9 @@ def make_desc(a: torch.Tensor, b: torch.Tensor, M: int, Nn: int, K: int, mode: i
               outf: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None, scale: float = 1.0,
               labels: Optional[torch.Tensor] = None, metrics_ptr: Optional[int] = None,
               block_n: int = 0, b_peers: Optional[Sequence[int]] = None,
-              k_bounds: Optional[Sequence[int]] = None) -> N.GemmDesc:
+              k_bounds: Optional[Sequence[int]] = None, upd_w: Optional[torch.Tensor] = None,
+              upd_ema: Optional[torch.Tensor] = None, upd_bias: Optional[torch.Tensor] = None,
+              upd_regularize: bool = False, a_slot_rows: int = 0, a_slots: int = 0) -> N.GemmDesc:
     """Describe one GEMM problem. ``a`` is [>=M, lda] and ``b`` is [>=N, ldb] bf16 storage; M/N/K are the
     logical extents (TMA zero-fills everything outside them)."""
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
@@ -62,6 +64,17 @@ def make_desc(a: torch.Tensor, b: torch.Tensor, M: int, Nn: int, K: int, mode: i
         assert labels.dtype == torch.int64
         d.labels = labels.data_ptr()
     d.metrics = metrics_ptr
+    if upd_w is not None:  # EPI_WGRAD_UPDATE: fp32 master / shadow [M, N] views of the flat buffers, fp32 bias copy
+        assert upd_w.dtype == torch.float32 and upd_w.stride(1) == 1
+        d.upd_w, d.ldf = upd_w.data_ptr(), upd_w.stride(0)
+        if outf is not None:
+            assert outf.stride(0) == upd_w.stride(0)
+        if upd_ema is not None:
+            assert upd_ema.dtype == torch.float32 and upd_ema.stride(0) == upd_w.stride(0)
+            d.upd_ema = upd_ema.data_ptr()
+        d.upd_bias = N.ptr(upd_bias)
+        d.upd_regularize = 1 if upd_regularize else 0
+    d.a_slot_rows, d.a_slots = int(a_slot_rows), int(a_slots)
     if b_peers:
         # pull-fused B: k range o of the operand is read from replica o's peer-mapped copy (K3)
         assert k_bounds is not None and len(k_bounds) == len(b_peers) + 1 and len(b_peers) <= N.MAX_PEERS
@@ -154,8 +167,47 @@ class GemmNet:
             N.check(rc if rc < 0 else -1, "ttd_gemm_net_build")
         self.ctas = rc
 
-    def launch(self, *, seed: int = 0, step_ptr: Optional[int] = None, pdl: bool = False) -> None:
+    def launch(self, *, seed: int = 0, step_ptr: Optional[int] = None, pdl: bool = False,
+               hyper: Optional[N.Hyper] = None, lr_slot: Optional[int] = None, state_ptr: Optional[int] = None,
+               finalize: int = 0) -> None:
+        """``hyper`` / ``lr_slot`` / ``state_ptr`` serve EPI_WGRAD_UPDATE problems (the optimiser step in the
+        weight-gradient epilogue); ``finalize`` bit0: the last CTA ends the training step, bit1: ++global_step."""
         lib = N.load()
-        N.check(lib.ttd_gemm_net_launch(self.ptr, self.n, self.grid, self.MAX_TASKS, self.ctas,
-                                        C.c_uint64(seed & (2**64 - 1)), step_ptr, 1 if pdl else 0, N.cur_stream()),
+        N.check(lib.ttd_gemm_net_launch_ex(self.ptr, self.n, self.grid, self.MAX_TASKS, self.ctas,
+                                           C.c_uint64(seed & (2**64 - 1)), step_ptr, 1 if pdl else 0,
+                                           C.byref(hyper) if hyper is not None else None, lr_slot, state_ptr,
+                                           int(finalize), N.cur_stream()),
                 "ttd_gemm_net_launch")
+
+
+class MlpColumn:
+    """Forward + loss + data gradients of a narrow MLP as ONE launch (``mlp_column_kernel``): a CTA owns 16 examples
+    through every layer, activations stay in shared memory. ``desc`` is a filled :class:`N.ColumnDesc`."""
+
+    def __init__(self, desc: N.ColumnDesc):
+        self.lib = N.load()
+        self._desc = desc  # keeps the pointers' owners findable while debugging; the handle has its own copy
+        self.handle = self.lib.ttd_mlp_column_create(C.byref(desc))
+        if not self.handle:
+            raise N.NativeError("ttd_mlp_column_create failed: " + self.lib.ttd_last_error().decode(errors="replace"))
+
+    def launch(self, *, seed: int = 0, pdl: bool = False) -> None:
+        N.check(self.lib.ttd_mlp_column_launch(self.handle, C.c_uint64(seed & (2**64 - 1)), 1 if pdl else 0,
+                                               N.cur_stream()), "ttd_mlp_column_launch")
+
+    def close(self) -> None:
+        if self.handle:
+            self.lib.ttd_mlp_column_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):  # noqa: D105
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+
+def column_fits(input_dim: int, layer_sizes: Sequence[int]) -> bool:
+    lib = N.load()
+    arr = (C.c_int32 * len(layer_sizes))(*[int(x) for x in layer_sizes])
+    return bool(lib.ttd_mlp_column_fits(int(input_dim), arr, len(layer_sizes)))

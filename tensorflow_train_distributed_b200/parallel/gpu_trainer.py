@@ -77,6 +77,9 @@ class GpuTrainer:
                                        pull_fused_first=self.sync and self.world > 1 and cfg.pull_fused and not lenet,
                                        tail_groups=tail)
             self.model = self._build_model()
+            if cfg.step_impl == "column" and not getattr(self.model, "use_column", False):
+                raise ValueError("--step_impl=column: this model / configuration does not fit the column kernel (narrow MLP "
+                                 "stacks only: hidden widths <= 256, <= 32 classes, no --fused_tail / --pull_fused)")
             # ring of step states written by the device itself (TtdHyper.host_mirror): slot = step index % RING
             self._pinned_state = torch.zeros(self.RING, 8, dtype=torch.int64).pin_memory()
             self._pinned_probe = torch.zeros(8, dtype=torch.int64).pin_memory()  # explicit read-backs (slot -1)
@@ -86,7 +89,7 @@ class GpuTrainer:
             B, F = self.model.x.shape
             self._feed_x = torch.zeros(2, B, F, device=self.device, dtype=torch.float32)
             self._feed_y = torch.zeros(2, B, device=self.device, dtype=torch.int64)
-            self.model.set_device_dataset(self._feed_x, self._feed_y)
+            self._feed_prep = self._attach_feed_pool()
         self.copy_stream = torch.cuda.Stream(device=self.device)
         self.lib = N.load()
         self.lib.ttd_set_barrier_timeout_ms(int(max(1.0, cfg.barrier_timeout_secs) * 1000))
@@ -95,6 +98,7 @@ class GpuTrainer:
             self._feed_y[0].data_ptr(), self._feed_y[1].data_ptr(), self._feed_x[0].numel() * 4, self._feed_y[0].numel() * 8)
         if not self._feeder:
             raise N.NativeError("ttd_feeder_create failed: " + self.lib.ttd_last_error().decode(errors="replace"))
+        self._configure_feeder_prep()
         self._host_keep = [None, None]
         import collections as _collections
         self._inflight = _collections.deque()
@@ -128,7 +132,8 @@ class GpuTrainer:
             return mlp_model.GpuMlp(self.store, cfg.batch_size, activation=cfg.activation,
                                     dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank, pdl=cfg.pdl,
                                     chain=cfg.fused_tail and cfg.tail_impl == "chain",
-                                    net=cfg.fused_tail and cfg.tail_impl == "net")
+                                    net=cfg.fused_tail and cfg.tail_impl == "net",
+                                    column=cfg.step_impl != "layers" and not cfg.fused_tail)
         from ..models import lenet
         return lenet.GpuLeNet(self.store, cfg.batch_size, activation=cfg.activation,
                               dropout_rate=cfg.dropout_rate, seed=cfg.seed + 7919 * self.rank, pdl=cfg.pdl,
@@ -193,15 +198,38 @@ class GpuTrainer:
         self._graph = g
         self._graph_exec = int(g.raw_cuda_graph_exec())  # launched by the native feeder (ttd_feeder_step)
 
+    def _attach_feed_pool(self):
+        """Point the model at the two-slot feed pool. Models that want their input pre-converted (column mode of
+        the MLP) return the conversion targets; the native feeder then converts each slot on the copy stream."""
+        set_feed = getattr(self.model, "set_feed_pool", None)
+        if set_feed is not None:
+            return set_feed(self._feed_x, self._feed_y)
+        self.model.set_device_dataset(self._feed_x, self._feed_y)
+        return None
+
+    def _configure_feeder_prep(self) -> None:
+        prep = self._feed_prep
+        B, F = self.model.x.shape
+        if prep is None:
+            N.check(self.lib.ttd_feeder_set_prep(self._feeder, B, F, None, 0, None, 0), "ttd_feeder_set_prep")
+        else:
+            xb, ldx, xT, ldt = prep
+            N.check(self.lib.ttd_feeder_set_prep(self._feeder, B, F, xb.data_ptr(), ldx, xT.data_ptr(), ldt),
+                    "ttd_feeder_set_prep")
+
     def use_device_dataset(self, x_pool, labels_pool) -> None:
         """Switch between a device-resident data set ([P,B,F] / [P,B], batch picked on the device from the
         local step) and host-fed batches (``None``); the step graph is re-captured for the new source."""
         self.stream.synchronize()
         self.copy_stream.synchronize()
         self._user_pool = x_pool is not None
-        if x_pool is None:
-            x_pool, labels_pool = self._feed_x, self._feed_y
-        self.model.set_device_dataset(x_pool, labels_pool)
+        with torch.cuda.stream(self.stream):
+            if x_pool is None:
+                self._feed_prep = self._attach_feed_pool()
+                self._configure_feeder_prep()
+            else:
+                self.model.set_device_dataset(x_pool, labels_pool)
+            self.stream.synchronize()
         if self._graph is not None:
             self._capture()
 

@@ -114,6 +114,8 @@ class GpuParamStore:
         f32c = raw[o_f32:o_f32 + f32_elems * 4].view(torch.float32)
         self.ema = raw[o_ema:o_ema + total * 4].view(torch.float32)
         self.state = raw[o_state:o_state + 64].view(torch.int64)  # TtdStepState (64 B)
+        # this step's learning rate and EMA decay, written by the column kernel for the fused update epilogue
+        self.lr_slot = raw[o_state + 64:o_state + 72].view(torch.float32)
         self._off = dict(grads=o_grads, w=o_w, ema=o_ema, state=o_state)
 
         self.w_rm: List[Optional[torch.Tensor]] = []
@@ -237,6 +239,23 @@ class GpuParamStore:
     def grad_matrix(self, i: int) -> torch.Tensor:
         g = self.layout.groups[i]
         return self.grads[g.offset:g.offset + g.numel].view(g.rows + 1, g.cols)
+
+    def master_matrix(self, i: int) -> torch.Tensor:
+        """fp32 master of group ``i`` as the [rows+1, cols] matrix (kernel rows, then the bias row)."""
+        g = self.layout.groups[i]
+        return self.w[g.offset:g.offset + g.numel].view(g.rows + 1, g.cols)
+
+    def ema_matrix(self, i: int) -> torch.Tensor:
+        g = self.layout.groups[i]
+        return self.ema[g.offset:g.offset + g.numel].view(g.rows + 1, g.cols)
+
+    @property
+    def hyper_native(self) -> N.Hyper:
+        return self._hyper_native
+
+    @property
+    def global_step_ptr(self) -> int:
+        return self.state.data_ptr() + N.OFF_GLOBAL_STEP
 
     @property
     def state_ptr(self) -> int:

@@ -30,16 +30,19 @@ def _torch_reference(vars_, x, y, sizes, act="elu"):
     return loss.item(), (h.argmax(1) == y).float().mean().item(), ws, bs
 
 
-@pytest.mark.parametrize("act,tail", [("elu", "chain"), ("relu", "chain"), ("elu", "cluster"), ("relu", "none")])
+@pytest.mark.parametrize("act,tail", [("elu", "chain"), ("relu", "chain"), ("elu", "cluster"), ("relu", "none"),
+                                      ("elu", "column"), ("relu", "column")])
 def test_step_gradients_match_autograd(act, tail):
-    """All back ends of the narrow layers: the single-CTA tcgen05 chain kernel, the fp32 cluster kernel and one
-    tcgen05 GEMM launch per layer."""
+    """All back ends of the narrow layers: the column kernel (activations resident in shared memory), the single-CTA
+    tcgen05 chain kernel, the fp32 cluster kernel and one tcgen05 GEMM launch per layer."""
     from tensorflow_train_distributed_b200.data import synthetic_mnist
     from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
-    cfg = _cfg(dropout_rate=0.0, cuda_graph=False, activation=act, fused_tail=tail != "none",
-               tail_impl=tail if tail != "none" else "chain")
+    cfg = _cfg(dropout_rate=0.0, cuda_graph=False, activation=act, fused_tail=tail not in ("none", "column"),
+               tail_impl=tail if tail not in ("none", "column") else "chain",
+               step_impl="column" if tail == "column" else "layers")
     tr = GpuTrainer(cfg)
     tr.initialize()
+    assert tr.model.use_column == (tail == "column")
     ds = synthetic_mnist(1024, seed=5)
     xs, ys = ds.next_batch(128)
     vars_ = tr.export_variables()
@@ -71,10 +74,14 @@ def test_graph_replay_equals_eager_and_learns():
     a = GpuTrainer(_cfg(cuda_graph=True))
     b = GpuTrainer(_cfg(cuda_graph=False))
     a.initialize(), b.initialize()
-    assert a.launches_per_step == 12  # prep + 5 fwd + 5 bwd + update: every layer is its own GEMM launch
+    assert a.launches_per_step == 2   # column kernel (forward + loss + data gradients) + weight gradients with the update
     c = GpuTrainer(_cfg(cuda_graph=False, fused_tail=True))
     c.initialize()
     assert c.launches_per_step == 5   # prep + first-layer fwd + chain kernel + first-layer wgrad + update
+    c.close()
+    c = GpuTrainer(_cfg(cuda_graph=False, step_impl="layers"))
+    c.initialize()
+    assert c.launches_per_step == 12  # prep + 5 fwd + 5 bwd + update: every layer is its own GEMM launch
     c.close()
     la = lb = None
     first = None
@@ -212,7 +219,7 @@ def test_fused_tail_follows_the_per_layer_path_with_dropout():
     from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
     ds1, ds2 = synthetic_mnist(4096, seed=6), synthetic_mnist(4096, seed=6)
     a = GpuTrainer(_cfg(dropout_rate=0.2, fused_tail=True, tail_impl="cluster"))
-    b = GpuTrainer(_cfg(dropout_rate=0.2, fused_tail=False))
+    b = GpuTrainer(_cfg(dropout_rate=0.2, fused_tail=False, step_impl="layers"))
     a.initialize(), b.initialize()
     for i in range(40):
         xa, ya = ds1.next_batch(128)
@@ -229,6 +236,46 @@ def test_fused_tail_follows_the_per_layer_path_with_dropout():
     a.close(), b.close()
 
 
+@pytest.mark.parametrize("batch,hidden", [(128, "200,100,50,25,10"), (100, "203,97,31,10"), (256, "64,10")])
+def test_column_kernel_follows_the_per_layer_path_with_dropout(batch, hidden):
+    """The column kernel draws the same Philox dropout masks and rounds to bf16 at the same places as one GEMM launch
+    per layer; what differs is the summation order inside the softmax and the operand roles of the MMAs. With equal
+    seeds the two trajectories therefore agree to rounding noise — on the reference shape, on a ragged one (batch 100,
+    widths that are no multiples of 8) and on two clusters' worth of batch."""
+    from tensorflow_train_distributed_b200.data import synthetic_mnist
+    from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
+    hu = [int(x) for x in hidden.split(",")]
+    ds1, ds2 = synthetic_mnist(4096, seed=6), synthetic_mnist(4096, seed=6)
+    a = GpuTrainer(_cfg(dropout_rate=0.1, batch_size=batch, hidden_units=hu, step_impl="column"))
+    b = GpuTrainer(_cfg(dropout_rate=0.1, batch_size=batch, hidden_units=hu, step_impl="layers"))
+    a.initialize(), b.initialize()
+    assert a.model.use_column and not b.model.use_column and a.launches_per_step == 2
+    for i in range(30):
+        va, vb = a.train_step(*ds1.next_batch(batch)), b.train_step(*ds2.next_batch(batch))
+        if i == 0:
+            assert abs(va.loss - vb.loss) < 2e-3 * max(1.0, vb.loss), (va.loss, vb.loss)
+            assert abs(va.accuracy - vb.accuracy) <= 1.5 / batch
+    assert va.global_step == vb.global_step == 30 and va.local_step == 30
+    assert abs(va.loss - vb.loss) < 2e-2 * max(1.0, vb.loss), (va.loss, vb.loss)
+    assert abs(va.learning_rate - vb.learning_rate) < 1e-9
+    wa, wb = a.export_variables(), b.export_variables()
+    assert set(wa) == set(wb)
+    for k in wa:
+        if k == "global_step":
+            continue
+        scale = max(float(np.abs(wb[k]).max()), 1e-6)
+        assert float(np.abs(wa[k] - wb[k]).max()) < 2e-2 * scale, (k, float(np.abs(wa[k] - wb[k]).max()), scale)
+    # the compute copies are what the next forward reads: they must be the bf16 image of the fp32 master
+    st = a.store
+    for i, g in enumerate(st.layout.groups):
+        m = st.master_matrix(i)
+        assert torch.equal(st.w_t[i][:, :g.rows], m[:g.rows].t().to(torch.bfloat16))
+        if st.w_rm[i] is not None:
+            assert torch.equal(st.w_rm[i][:, :g.cols], m[:g.rows].to(torch.bfloat16))
+        assert torch.equal(st.bias_c[i][:g.cols], m[g.rows])
+    a.close(), b.close()
+
+
 def test_chain_kernel_is_bitwise_the_per_layer_path():
     """The chain kernel runs the very same tcgen05 pipeline and epilogues as one launch per layer would: with
     identical seeds the two trainers must stay together to the last bit of the loss (atomics aside)."""
@@ -236,7 +283,7 @@ def test_chain_kernel_is_bitwise_the_per_layer_path():
     from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
     ds1, ds2 = synthetic_mnist(4096, seed=6), synthetic_mnist(4096, seed=6)
     a = GpuTrainer(_cfg(dropout_rate=0.1, fused_tail=True, tail_impl="chain"))
-    b = GpuTrainer(_cfg(dropout_rate=0.1, fused_tail=False))
+    b = GpuTrainer(_cfg(dropout_rate=0.1, fused_tail=False, step_impl="layers"))
     a.initialize(), b.initialize()
     assert a.launches_per_step == 5 and b.launches_per_step == 12
     for _ in range(30):
@@ -257,7 +304,7 @@ def test_net_kernel_is_bitwise_the_per_layer_path():
     from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
     ds1, ds2 = synthetic_mnist(4096, seed=6), synthetic_mnist(4096, seed=6)
     a = GpuTrainer(_cfg(dropout_rate=0.1, fused_tail=True, tail_impl="net"))
-    b = GpuTrainer(_cfg(dropout_rate=0.1, fused_tail=False))
+    b = GpuTrainer(_cfg(dropout_rate=0.1, fused_tail=False, step_impl="layers"))
     a.initialize(), b.initialize()
     assert a.launches_per_step == 3 and b.launches_per_step == 12  # prep + net + update
     assert a.model._net.ctas == 114  # one CTA per tile for the reference model

@@ -7,7 +7,7 @@ from tensorflow_train_distributed_b200.config import TrainConfig
 from tensorflow_train_distributed_b200.ops import _native as N
 from tensorflow_train_distributed_b200.parallel.gpu_trainer import GpuTrainer
 
-cfg = TrainConfig(worker_hosts="127.0.0.1:2222", save_checkpoint_secs=None, cuda_graph=False)
+cfg = TrainConfig(worker_hosts="127.0.0.1:2222", save_checkpoint_secs=None, cuda_graph=False, step_impl="layers")
 tr = GpuTrainer(cfg)
 tr.initialize()
 lib = N.load()

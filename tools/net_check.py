@@ -42,7 +42,7 @@ def main():
     out = {}
     graph = os.environ.get("NET_GRAPH", "1") == "1"
     a = GpuTrainer(cfg(dropout_rate=0.1, fused_tail=True, tail_impl="net", cuda_graph=graph))
-    b = GpuTrainer(cfg(dropout_rate=0.1, fused_tail=False, cuda_graph=graph))
+    b = GpuTrainer(cfg(dropout_rate=0.1, fused_tail=False, step_impl="layers", cuda_graph=graph))
     a.initialize(), b.initialize()
     out["launches"] = [a.launches_per_step, b.launches_per_step]
     out["net_ctas"] = getattr(a.model, "_net", None).ctas if hasattr(a.model, "_net") else a.model.head._net.ctas
