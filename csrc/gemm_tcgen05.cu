@@ -1253,6 +1253,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_net_kernel(const GemmProblem
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   }
+  if (h.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) h.trace[4 * kNetMaxProblems] = globaltimer_ns();
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -1400,6 +1401,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_net_kernel(const GemmProblem
       __threadfence();
       if ((h.finalize & 1) && h.state != nullptr)  // this launch ends the training step
         finalize_step(h.state, h.hyper, h.lr_slot != nullptr ? h.lr_slot[0] : 0.0f, (h.finalize & 2) != 0);
+      if (h.trace != nullptr) h.trace[4 * kNetMaxProblems + 1] = globaltimer_ns();
     }
   }
 }

@@ -91,6 +91,8 @@ struct ColParams {
   const long long* global_step_ptr;
   float* lr_out;
   TtdHyper hyper;
+  unsigned long long* trace;  // optional (CTA 0): [0] dependency resolved, [1+2t] accumulator of stage t ready,
+                              // [2+2t] stage t's epilogue stored, [63] kernel end — globaltimer ns
 };
 
 // byte offset of element (example n, feature f) inside a [16 x K] K-major, 128-byte-swizzled operand buffer
@@ -171,6 +173,8 @@ __global__ void __launch_bounds__(kColThreads, 1) mlp_column_kernel(const __grid
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   }
+  unsigned long long* tr = (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) ? p.trace : nullptr;
+  if (tr) tr[0] = globaltimer_ns();
   const unsigned long long step = p.step_ptr != nullptr ? *p.step_ptr : 0ull;
   const int slot = p.pool_batches > 1 ? static_cast<int>(step % static_cast<unsigned long long>(p.pool_batches)) : 0;
   const int n_stages = 2 * L - 1;  // L forward stages, L-1 data-gradient stages
@@ -338,6 +342,7 @@ __global__ void __launch_bounds__(kColThreads, 1) mlp_column_kernel(const __grid
       }
       mbar_wait(acc_bar, static_cast<uint32_t>(t & 1));
       tc_fence_after();
+      if (tr) tr[1 + 2 * t] = globaltimer_ns();
 
       if (fwd && l < L - 1) {
         // ---------------- hidden layer: bias + activation + dropout -> next operand (smem) + aT (global) -----
@@ -440,6 +445,7 @@ __global__ void __launch_bounds__(kColThreads, 1) mlp_column_kernel(const __grid
           }
         }
       }
+      if (tr) tr[2 + 2 * t] = globaltimer_ns();
       if (t + 1 < n_stages) {
         fence_proxy_async();   // generic-proxy stores to the operand buffer -> visible to the tensor core's reads
         tc_fence_before();     // this warp's tcgen05.ld are ordered before the MMA thread's next tcgen05.mma
@@ -451,6 +457,7 @@ __global__ void __launch_bounds__(kColThreads, 1) mlp_column_kernel(const __grid
 
   tc_fence_before();
   __syncthreads();
+  if (tr) tr[63] = globaltimer_ns();
   if (cl > 1) cluster_sync_all();  // nobody leaves while a peer's commit may still signal one of its barriers
   if (warp == kWarpAux) {
     tc_fence_after();
@@ -618,6 +625,10 @@ extern "C" void* ttd_mlp_column_create(const TtdColumnDesc* d) {
   return h;
 }
 
+static unsigned long long* g_col_trace = nullptr;
+// Diagnostic: device buffer of 64 uint64 that receives CTA 0's stage timestamps (NULL switches it off).
+extern "C" void ttd_mlp_column_set_trace(void* device_buf) { g_col_trace = static_cast<unsigned long long*>(device_buf); }
+
 extern "C" void ttd_mlp_column_destroy(void* handle) { delete static_cast<ColumnHandle*>(handle); }
 
 extern "C" int ttd_mlp_column_launch(void* handle, uint64_t seed, uint32_t flags, void* stream) {
@@ -636,6 +647,7 @@ extern "C" int ttd_mlp_column_launch(void* handle, uint64_t seed, uint32_t flags
   h->p.seed_lo = static_cast<uint32_t>(seed);
   h->p.seed_hi = static_cast<uint32_t>(seed >> 32);
   h->p.use_pdl = (flags & 1u) ? 1 : 0;
+  h->p.trace = g_col_trace;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(static_cast<unsigned>(h->grid));

@@ -286,6 +286,8 @@ void* ttd_mlp_column_create(const TtdColumnDesc* desc_host);
 void ttd_mlp_column_destroy(void* handle);
 /* flags bit0: programmatic dependent launch. */
 int ttd_mlp_column_launch(void* handle, uint64_t seed, uint32_t flags, void* stream);
+/* Diagnostic: device buffer of 64 uint64 receiving CTA 0's stage timestamps (globaltimer ns); NULL = off. */
+void ttd_mlp_column_set_trace(void* device_buf_64_u64);
 /* 1 if a model of these sizes fits the kernel (hidden widths, class count, shared memory), else 0. */
 int ttd_mlp_column_fits(int32_t input_dim, const int32_t* layer_sizes, int32_t n_layers);
 
@@ -328,6 +330,7 @@ int ttd_gemm_net_launch(const void* device_buf, int count, int grid, int max_tas
 int ttd_gemm_net_launch_ex(const void* device_buf, int count, int grid, int max_tasks, int ctas, uint64_t seed,
                            const uint64_t* step_ptr, uint32_t flags, const TtdHyper* hyper_host, const float* lr_slot,
                            TtdStepState* state, int32_t finalize, void* stream);
+/* trace buffer: 4 uint64 per problem (24 problems max) + [96] kernel start after the dependency, [97] last CTA done */
 void ttd_gemm_net_set_trace(void* device_buf_4_u64_per_problem);
 
 /* ---- step feeder: the host side of a training step in one native call (reference: the C++ session run loop

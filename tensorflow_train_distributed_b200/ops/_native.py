@@ -232,6 +232,8 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.ttd_mlp_column_destroy.argtypes = [C.c_void_p]
     lib.ttd_mlp_column_launch.restype = C.c_int
     lib.ttd_mlp_column_launch.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p]
+    lib.ttd_mlp_column_set_trace.restype = None
+    lib.ttd_mlp_column_set_trace.argtypes = [C.c_void_p]
     lib.ttd_mlp_column_fits.restype = C.c_int
     lib.ttd_mlp_column_fits.argtypes = [C.c_int32, C.POINTER(C.c_int32), C.c_int32]
     lib.ttd_gemm_net_set_trace.restype = None
